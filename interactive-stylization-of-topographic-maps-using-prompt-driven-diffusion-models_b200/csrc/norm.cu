@@ -1,0 +1,248 @@
+// K4 GroupNorm(+SiLU) and K8 LayerNorm — the HBM-bound normalisation kernels of the path.
+// NHWC bf16 in/out, statistics in fp32 (GroupNorm32 upcasts upstream), 16-byte accesses, every pixel row read
+// fully coalesced (all channels of a pixel are contiguous).
+//   groupnorm: pass 1 = per-(sample, slab) partial sums per group (deterministic, no global atomics),
+//              pass 2 = per-channel scale/shift in smem, then one streaming read + write.
+//              The second read of x hits L2 (a sample's activation is at most a few MB of the 126 MB L2).
+//   layernorm: one warp per row, the row is held in registers (C <= 2048), exact two-pass variance.
+#include "common.cuh"
+#include "topo_b200.h"
+
+namespace topo {
+
+constexpr int GN_THREADS = 256;
+constexpr int GN_MAX_SPLITS = 256;
+constexpr int GN_MAX_C = 4096;
+
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
+  f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
+}
+
+// grid (splits, B). Block handles pixels [split*ppb, min(HW, (split+1)*ppb)) of sample b.
+__global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __restrict__ x, int x_ld, int HW, int C, int G,
+                                                             int ppb, float* __restrict__ ws) {
+  extern __shared__ float sh[];  // [2*C] per-channel sum, sumsq
+  float* ch_sum = sh;
+  float* ch_sq = sh + C;
+  for (int i = threadIdx.x; i < 2 * C; i += GN_THREADS) sh[i] = 0.f;
+  __syncthreads();
+  const int b = blockIdx.y, split = blockIdx.x;
+  const int vpr = C >> 3;  // 16-byte vectors per pixel row
+  const int p0 = split * ppb;
+  const int p1 = min(HW, p0 + ppb);
+  const bf16* xb = x + (size_t)b * HW * x_ld;
+  // thread -> fixed channel vector when possible (vpr divides the stride), generic otherwise
+  const int total = (p1 - p0) * vpr;
+  if (GN_THREADS % vpr == 0) {
+    const int v = threadIdx.x % vpr;
+    const int prow = threadIdx.x / vpr, pstep = GN_THREADS / vpr;
+    float s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+    for (int pp = p0 + prow; pp < p1; pp += pstep) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
+      float f[8];
+      unpack8(u, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += f[i];
+        q[i] = fmaf(f[i], f[i], q[i]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      atomicAdd(&ch_sum[v * 8 + i], s[i]);
+      atomicAdd(&ch_sq[v * 8 + i], q[i]);
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < total; idx += GN_THREADS) {
+      const int pp = p0 + idx / vpr, v = idx % vpr;
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
+      float f[8];
+      unpack8(u, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        atomicAdd(&ch_sum[v * 8 + i], f[i]);
+        atomicAdd(&ch_sq[v * 8 + i], f[i] * f[i]);
+      }
+    }
+  }
+  __syncthreads();
+  const int cpg = C / G;
+  for (int g = threadIdx.x; g < G; g += GN_THREADS) {
+    float s = 0.f, q = 0.f;
+    for (int i = 0; i < cpg; ++i) {
+      s += ch_sum[g * cpg + i];
+      q += ch_sq[g * cpg + i];
+    }
+    float* o = ws + (((size_t)b * gridDim.x + split) * G + g) * 2;
+    o[0] = s;
+    o[1] = q;
+  }
+}
+
+// grid (splits2, B)
+__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+                                                             int y_ld, int HW, int C, int G, int ppb, int nsplit_stats,
+                                                             const float* __restrict__ ws,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps, int apply_silu) {
+  extern __shared__ float sh[];  // [2*C] scale, shift ; [2*G] mean, rstd
+  float* sc = sh;
+  float* sf = sh + C;
+  float* mr = sh + 2 * C;
+  const int b = blockIdx.y;
+  const int cpg = C / G;
+  for (int g = threadIdx.x; g < G; g += GN_THREADS) {
+    float s = 0.f, q = 0.f;
+    for (int k = 0; k < nsplit_stats; ++k) {
+      const float* w = ws + (((size_t)b * nsplit_stats + k) * G + g) * 2;
+      s += w[0];
+      q += w[1];
+    }
+    const float n = (float)HW * cpg;
+    const float mean = s / n;
+    const float var = fmaxf(q / n - mean * mean, 0.f);
+    mr[2 * g] = mean;
+    mr[2 * g + 1] = rsqrtf(var + eps);
+  }
+  __syncthreads();
+  for (int ch = threadIdx.x; ch < C; ch += GN_THREADS) {
+    const int g = ch / cpg;
+    const float a = gamma[ch] * mr[2 * g + 1];
+    sc[ch] = a;
+    sf[ch] = beta[ch] - mr[2 * g] * a;
+  }
+  __syncthreads();
+  const int vpr = C >> 3;
+  const int p0 = blockIdx.x * ppb;
+  const int p1 = min(HW, p0 + ppb);
+  const int total = (p1 - p0) * vpr;
+  const bf16* xb = x + (size_t)b * HW * x_ld;
+  bf16* yb = y + (size_t)b * HW * y_ld;
+  for (int idx = threadIdx.x; idx < total; idx += GN_THREADS) {
+    const int pp = p0 + idx / vpr, v = idx % vpr;
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
+    float f[8];
+    unpack8(u, f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float t = fmaf(f[i], sc[v * 8 + i], sf[v * 8 + i]);
+      f[i] = apply_silu ? silu_f(t) : t;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+    *(reinterpret_cast<uint4*>(yb + (size_t)pp * y_ld) + v) = o;
+  }
+}
+
+static int gn_splits(int B, int HW) {
+  int s = (4 * 148 + B - 1) / B;  // ~4 CTAs per SM across the batch
+  if (s > GN_MAX_SPLITS) s = GN_MAX_SPLITS;
+  if (s > HW) s = HW;
+  if (s < 1) s = 1;
+  return s;
+}
+
+int groupnorm_ws_floats(int B, int G) { return B * G * 2 * GN_MAX_SPLITS; }
+
+int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int B, int HW,
+                       int C, int G, float eps, int apply_silu, float* ws, cudaStream_t st) {
+  TOPO_CHECK(C % 8 == 0 && C % G == 0 && C <= GN_MAX_C, TOPO_E_INVAL, "groupnorm: C=%d G=%d unsupported", C, G);
+  TOPO_CHECK(x_ld % 8 == 0 && y_ld % 8 == 0, TOPO_E_INVAL, "groupnorm: leading dims must be multiples of 8");
+  TOPO_CHECK(ws != nullptr, TOPO_E_INVAL, "groupnorm: workspace required");
+  const int splits = gn_splits(B, HW);
+  const int ppb = (HW + splits - 1) / splits;
+  const int nsplit = (HW + ppb - 1) / ppb;
+  dim3 grid(nsplit, B);
+  gn_stats_kernel<<<grid, GN_THREADS, 2 * C * sizeof(float), st>>>(reinterpret_cast<const bf16*>(x), x_ld, HW, C, G, ppb, ws);
+  gn_apply_kernel<<<grid, GN_THREADS, (2 * C + 2 * G) * sizeof(float), st>>>(
+      reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), y_ld, HW, C, G, ppb, nsplit, ws, gamma, beta,
+      eps, apply_silu);
+  TOPO_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// LayerNorm: one warp per row
+// ------------------------------------------------------------------------------------------------
+template <int MAXV>
+__global__ void __launch_bounds__(256) layernorm_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+                                                       int y_ld, int M, int C, const float* __restrict__ gamma,
+                                                       const float* __restrict__ beta, float eps) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= M) return;
+  const int vpr = C >> 3;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)row * x_ld);
+  float f[MAXV][8];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < MAXV; ++k) {
+    const int v = lane + k * 32;
+    if (v < vpr) {
+      unpack8(__ldg(xr + v), f[k]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += f[k][i];
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / C;
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < MAXV; ++k) {
+    const int v = lane + k * 32;
+    if (v < vpr) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = f[k][i] - mean;
+        q = fmaf(d, d, q);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q / C + eps);
+  uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * y_ld);
+#pragma unroll
+  for (int k = 0; k < MAXV; ++k) {
+    const int v = lane + k * 32;
+    if (v < vpr) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v);
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v + 1);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v);
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v + 1);
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float r[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) r[i] = fmaf((f[k][i] - mean) * rstd, gg[i], bb[i]);
+      uint4 o;
+      o.x = pack_bf16x2(r[0], r[1]); o.y = pack_bf16x2(r[2], r[3]);
+      o.z = pack_bf16x2(r[4], r[5]); o.w = pack_bf16x2(r[6], r[7]);
+      yr[v] = o;
+    }
+  }
+}
+
+int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int M, int C,
+                       float eps, cudaStream_t st) {
+  TOPO_CHECK(C % 8 == 0 && C <= 2048, TOPO_E_INVAL, "layernorm: C=%d unsupported (multiple of 8, <= 2048)", C);
+  TOPO_CHECK(x_ld % 8 == 0 && y_ld % 8 == 0, TOPO_E_INVAL, "layernorm: leading dims must be multiples of 8");
+  const int grid = (M + 7) / 8;
+  const bf16* xx = reinterpret_cast<const bf16*>(x);
+  bf16* yy = reinterpret_cast<bf16*>(y);
+  if (C <= 512)
+    layernorm_kernel<2><<<grid, 256, 0, st>>>(xx, x_ld, yy, y_ld, M, C, gamma, beta, eps);
+  else if (C <= 1280)
+    layernorm_kernel<5><<<grid, 256, 0, st>>>(xx, x_ld, yy, y_ld, M, C, gamma, beta, eps);
+  else
+    layernorm_kernel<8><<<grid, 256, 0, st>>>(xx, x_ld, yy, y_ld, M, C, gamma, beta, eps);
+  TOPO_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace topo

@@ -1,0 +1,108 @@
+"""-m gpu: the tcgen05 projection GEMM family (K1/K5/K6/K7/K9) through the C ABI vs fp32 torch math.
+Tolerance: outputs are bf16 (8 mantissa bits) of fp32-accumulated bf16 products -> relative 1e-2 of the
+tensor's max magnitude (the LoRA branch adds one extra bf16 rounding of s*T)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from gpu_util import BF16, assert_close, bf, rnd
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-2
+
+
+def _ops():
+    from topo_b200 import ops
+    return ops
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 128), (300, 320, 320), (8192, 320, 960), (154, 768, 384), (64, 1280, 1280)])
+def test_gemm_plain(M, K, N):
+    ops = _ops()
+    x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
+    y = ops.linear(x, W)
+    assert_close(y, x.float() @ W.float().t(), TOL, f"gemm {M}x{K}x{N}")
+
+
+def test_gemm_bias_res_silu_fp32out():
+    ops = _ops()
+    M, K, N = 520, 640, 328
+    x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
+    b, res = rnd(N, seed=3), rnd(M, N, seed=4).to(BF16)
+    y = ops.linear(x, W, b, res=res, act=ops.ACT_SILU, alpha=0.7, out_fp32=True)
+    ref = 0.7 * F.silu(x.float() @ W.float().t() + b) + res.float()
+    assert y.dtype == torch.float32
+    assert_close(y, ref, TOL, "gemm bias+silu+alpha+res fp32")
+
+
+def test_gemm_geglu():
+    ops = _ops()
+    M, K, inner = 1000, 320, 1280
+    x, W, b = rnd(M, K, seed=1).to(BF16), rnd(2 * inner, K, seed=2, scale=K ** -0.5).to(BF16), rnd(2 * inner, seed=3)
+    y = ops.linear(x, W, b, act=ops.ACT_GEGLU)
+    h = x.float() @ W.float().t() + b
+    a, g = h.chunk(2, -1)
+    assert y.shape == (M, inner)
+    assert_close(y, a * F.gelu(g), TOL, "gemm GEGLU")
+
+
+@pytest.mark.parametrize("r", [4, 12, 16, 32])
+def test_lora_linear(r):
+    """y = base(x) + B(A(x)) * s  — LoRA_modified/LoRA_utils.py:40-42."""
+    ops = _ops()
+    M, K, N, s = 1024 + 40, 320, 320, 2.0
+    x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
+    A, Bm = rnd(r, K, seed=3, scale=K ** -0.5).to(BF16), rnd(N, r, seed=4, scale=0.3).to(BF16)
+    b = rnd(N, seed=5)
+    y = ops.linear(x, W, b, A, Bm, s)
+    xf = x.float()
+    ref = xf @ W.float().t() + b + s * ((xf @ A.float().t()) @ Bm.float().t())
+    base = xf @ W.float().t() + b
+    assert (ref - base).abs().max() > 0.1, "LoRA delta must be non-trivial for the test to mean anything"
+    assert_close(y, ref, TOL, f"lora linear r={r}")
+
+
+def test_fused_qkv_three_segments():
+    """n_seg=3: one read of x, three (W, A, B, out) segments written into one [M, 3N] buffer."""
+    from topo_b200 import capi
+    ops = _ops()
+    M, K, N, r = 2048, 320, 384, 8
+    x = rnd(M, K, seed=1).to(BF16)
+    out = torch.zeros(M, 3 * N, dtype=BF16, device="cuda")
+    segs, refs, keep = [], [], []
+    for i in range(3):
+        W = rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16)
+        A, Bm = rnd(r, K, seed=20 + i, scale=K ** -0.5), rnd(N, r, seed=30 + i, scale=0.3)
+        Ap, Bp, rp = ops.prep_lora(A, Bm)
+        keep += [W, Ap, Bp]
+        segs.append(capi.make_linear(W, out, N, A=Ap, B=Bp, r_pad=rp, s=2.0, out_ld=3 * N, out_col=i * N))
+        xf = x.float()
+        refs.append(xf @ W.float().t() + 2.0 * ((xf @ bf(A).t()) @ bf(Bm).t()))
+    ops.lora_linear_raw(x, M, K, K, segs)
+    assert_close(out, torch.cat(refs, 1), TOL, "fused qkv (3 segments)")
+
+
+def test_zeroconv_residual_into_concat_buffer():
+    """(e) out[:, off:off+C] = skip + scale*(h Wz^T + bz), other columns untouched."""
+    ops = _ops()
+    M, Cc, off, ld = 2048, 320, 640, 960
+    h, skip = rnd(M, Cc, seed=1).to(BF16), rnd(M, Cc, seed=2).to(BF16)
+    Wz, bz = rnd(Cc, Cc, seed=3, scale=0.05).to(BF16), rnd(Cc, seed=4)
+    out = torch.full((M, ld), 7.0, dtype=BF16, device="cuda")
+    ops.zeroconv_residual(h, Wz, bz, 0.5, skip, out, off)
+    ref = skip.float() + 0.5 * (h.float() @ Wz.float().t() + bz)
+    assert_close(out[:, off:off + Cc], ref, TOL, "zero-conv residual")
+    assert (out[:, :off] == 7.0).all(), "columns outside the slice were touched"
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(2, 64, 64, 320, 320), (2, 8, 8, 1280, 1280), (3, 16, 16, 640, 1280),
+                                            (1, 32, 32, 1920, 640), (1, 128, 128, 128, 128), (1, 64, 64, 320, 4)])
+def test_conv3x3_implicit_gemm(B, H, W, Cin, Cout):
+    ops = _ops()
+    x = rnd(B, H, W, Cin, seed=1).to(BF16)
+    w = rnd(Cout, Cin, 3, 3, seed=2, scale=(9 * Cin) ** -0.5).to(BF16)
+    b = rnd(Cout, seed=3)
+    emb = rnd(B, Cout, seed=4)
+    y = ops.conv3x3(x, w, b, rowbias=emb)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), b, padding=1) + emb[:, :, None, None]
+    assert_close(y.float().permute(0, 3, 1, 2), ref, TOL, f"conv3x3 {B}x{H}x{W} {Cin}->{Cout}")
