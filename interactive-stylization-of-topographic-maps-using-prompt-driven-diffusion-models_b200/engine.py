@@ -1,0 +1,625 @@
+"""TopoEngine — the execution plan of ``ControlLDM.apply_model`` / ``decode_first_stage`` on the sm_100a kernels.
+
+The module tree in ``ldm.py`` only holds parameters; this file walks it once (after every weight load / LoRA
+surgery), packs the weights into the layouts the kernels want (bf16, K-major, padded heads, GEGLU-interleaved,
+tap-major conv filters) and then executes a forward as a flat sequence of C-ABI calls.  PyTorch is used for
+device memory (``torch.empty``), dtype casts of inputs and the CUDA stream — no arithmetic.
+
+Data layout in HBM: activations are NHWC bf16, i.e. token matrices ``[B*H*W, C]`` (row-major, C contiguous);
+the residual stream, attention q/k/v (heads padded 40→48) and the decoder concat buffers ``[h | skip]`` are all
+token matrices, so "rearrange b c h w -> b (h w) c" and ``torch.cat`` cost nothing: producers write straight
+into a column slice (``out_ld`` / ``out_col`` of ``topo_linear_t``).
+
+Fusions (BASELINE.json north_star a–e):
+ (a) q/k/v in one launch (3 segments, one read of x), LoRA delta folded into the same tcgen05 GEMM
+ (b)/(c) flash attention on TMEM; cross-attention K/V are step-invariant and hoisted (``prepare``)
+ (d) GroupNorm+SiLU one op
+ (e) ControlNet zero-conv + ``hs.pop() + control.pop()`` + ``torch.cat`` = one GEMM epilogue writing the skip
+     half of the UNet decoder's concat buffer; ``h += control.pop()`` at the mid block likewise.
+Upstream semantics restated in SURVEY.md Appendix A; call sites: ``vis_metrics.py:437`` (sampling),
+``…_ctrlora.py:388`` / ``vis_metrics.py:112`` (apply_model), ``vis_metrics.py:450`` (decode).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import capi, ops
+from .capi import ACT_GEGLU, ACT_NONE, ACT_SILU, make_linear
+from .ops import BF16
+
+LAUNCHES = [0]  # number of libtopo_b200 kernels launched (bench.py reports it as gpu_launches)
+
+
+def _count(n: int = 1) -> None:
+    LAUNCHES[0] += n
+
+
+# ----------------------------------------------------------------------------------------------
+# packed weights
+# ----------------------------------------------------------------------------------------------
+@dataclass
+class Lin:
+    """One projection ``y = x W^T (+b) + s (x A^T) B^T`` packed for topo_lora_linear."""
+    W: torch.Tensor                       # bf16 [N, K]
+    bias: Optional[torch.Tensor]          # fp32 [N]
+    A: Optional[torch.Tensor] = None      # bf16 [rp, K]
+    B: Optional[torch.Tensor] = None      # bf16 [N, rp]
+    rp: int = 0
+    s: float = 1.0
+
+    @property
+    def N(self) -> int:
+        return self.W.shape[0]
+
+    @property
+    def K(self) -> int:
+        return self.W.shape[1]
+
+
+def _dev(t: Optional[torch.Tensor], device, dtype) -> Optional[torch.Tensor]:
+    return None if t is None else t.detach().to(device=device, dtype=dtype).contiguous()
+
+
+def pack_linear(mod: nn.Module, device, heads: int = 0, d: int = 0, dp: int = 0, pad: str = "") -> Lin:
+    """Pack an ``nn.Linear`` / ``LoRALinear`` / ``LoRACompatibleLinear``.  ``pad='rows'`` zero-pads the output
+    features per head (q/k/v: 40→48), ``pad='cols'`` the input features (to_out consumes the padded layout)."""
+    W, b, A, Bm, s = ops._proj_params(mod)
+    W = W.detach().to(device)
+    if A is not None:
+        A, Bm = A.detach().to(device), Bm.detach().to(device)
+    if b is not None:
+        b = b.detach().to(device)
+    if pad == "rows" and dp != d:
+        W = ops.pad_head_rows(W, heads, d, dp)
+        Bm = None if Bm is None else ops.pad_head_rows(Bm, heads, d, dp)
+        b = None if b is None else ops.pad_head_rows(b[:, None], heads, d, dp)[:, 0]
+    elif pad == "cols" and dp != d:
+        W = ops.pad_head_cols(W, heads, d, dp)
+        A = None if A is None else ops.pad_head_cols(A, heads, d, dp)
+    rp = 0
+    if A is not None:
+        A, Bm, rp = ops.prep_lora(A, Bm)
+    return Lin(W.to(BF16).contiguous(), _dev(b, device, torch.float32), A, Bm, rp, s)
+
+
+def pack_conv1x1(conv: nn.Conv2d, device) -> Lin:
+    W = conv.weight.detach().to(device).reshape(conv.out_channels, conv.in_channels)
+    return Lin(W.to(BF16).contiguous(), _dev(conv.bias, device, torch.float32))
+
+
+def pack_conv3x3(conv: nn.Conv2d, device) -> Lin:
+    return Lin(ops.conv3x3_weight(conv.weight.detach().to(device)), _dev(conv.bias, device, torch.float32))
+
+
+def pack_geglu(mod: nn.Module, device) -> Lin:
+    """GEGLU ``proj`` with rows interleaved per 128-row tile (64 values | 64 gates) for the fused epilogue."""
+    lin = pack_linear(mod, device)
+    inner, half = lin.N // 2, 64
+    idx = []
+    for t in range(inner // half):
+        idx += list(range(t * half, (t + 1) * half)) + list(range(inner + t * half, inner + (t + 1) * half))
+    idx = torch.tensor(idx, device=device)
+    lin.W = lin.W[idx].contiguous()
+    lin.bias = None if lin.bias is None else lin.bias[idx].contiguous()
+    lin.B = None if lin.B is None else lin.B[idx].contiguous()
+    return lin
+
+
+@dataclass
+class Norm:
+    gamma: torch.Tensor
+    beta: torch.Tensor
+    eps: float
+    groups: int = 0
+
+
+def pack_norm(m: nn.Module, device) -> Norm:
+    return Norm(_dev(m.weight, device, torch.float32), _dev(m.bias, device, torch.float32), float(m.eps),
+                int(getattr(m, "num_groups", 0)))
+
+
+# ----------------------------------------------------------------------------------------------
+# launch helpers (each = exactly one topo_* call)
+# ----------------------------------------------------------------------------------------------
+def gemm(x: torch.Tensor, lin: Lin, out: Optional[torch.Tensor] = None, out_col: int = 0,
+         res: Optional[torch.Tensor] = None, res_col: int = 0, act: int = ACT_NONE, alpha: float = 1.0,
+         rowbias: Optional[torch.Tensor] = None, rows_per_group: int = 1, out_fp32: bool = False) -> torch.Tensor:
+    """x [M, K] (row stride arbitrary) → out[:, out_col : out_col+N] ; returns ``out`` (allocated if None)."""
+    M = x.shape[0]
+    n_out = lin.N // 2 if act == ACT_GEGLU else lin.N
+    if out is None:
+        out = torch.empty(M, n_out, dtype=torch.float32 if out_fp32 else BF16, device=x.device)
+    seg = make_linear(lin.W, out, lin.N, bias=lin.bias, A=lin.A, B=lin.B, r_pad=lin.rp, s=lin.s, alpha=alpha,
+                      out_ld=out.stride(0), out_col=out_col, out_fp32=out_fp32, res=res,
+                      res_ld=0 if res is None else res.stride(0), res_col=res_col, rowbias=rowbias,
+                      rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=rows_per_group, act=act)
+    ops.lora_linear_raw(x, M, lin.K, x.stride(0), [seg])
+    _count()
+    return out
+
+
+def gemm_multi(x: torch.Tensor, lins: Sequence[Lin], out: torch.Tensor, cols: Sequence[int]) -> None:
+    """Several projections of the same x in ONE launch when their padded LoRA ranks agree, else one launch each."""
+    M = x.shape[0]
+    if len({l.rp for l in lins}) == 1 and len({l.K for l in lins}) == 1 and len(lins) <= 3:
+        segs = [make_linear(l.W, out, l.N, bias=l.bias, A=l.A, B=l.B, r_pad=l.rp, s=l.s, out_ld=out.stride(0),
+                            out_col=c) for l, c in zip(lins, cols)]
+        ops.lora_linear_raw(x, M, lins[0].K, x.stride(0), segs)
+        _count()
+    else:
+        for l, c in zip(lins, cols):
+            gemm(x, l, out, c)
+
+
+def conv3(x: torch.Tensor, B: int, H: int, W: int, lin: Lin, out: Optional[torch.Tensor] = None, out_col: int = 0,
+          res: Optional[torch.Tensor] = None, res_col: int = 0, rowbias: Optional[torch.Tensor] = None,
+          out_fp32: bool = False) -> torch.Tensor:
+    """3x3/s1/p1 implicit-GEMM conv on the token matrix x [B*H*W, C]."""
+    C = x.shape[1]
+    if out is None:
+        out = torch.empty(B * H * W, lin.N, dtype=torch.float32 if out_fp32 else BF16, device=x.device)
+    seg = make_linear(lin.W, out, lin.N, bias=lin.bias, out_ld=out.stride(0), out_col=out_col, out_fp32=out_fp32,
+                      res=res, res_ld=0 if res is None else res.stride(0), res_col=res_col, rowbias=rowbias,
+                      rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=H * W)
+    ops.conv3x3_raw(x, B, H, W, C, x.stride(0), seg)
+    _count()
+    return out
+
+
+def gn(x: torch.Tensor, B: int, n: Norm, silu: bool) -> torch.Tensor:
+    y = ops.groupnorm_silu(x.view(B, -1, x.shape[1]), n.gamma, n.beta, n.groups, n.eps, silu)
+    _count(2)
+    return y.view(x.shape)
+
+
+def ln(x: torch.Tensor, n: Norm) -> torch.Tensor:
+    _count()
+    return ops.layernorm(x, n.gamma, n.beta, n.eps)
+
+
+# ----------------------------------------------------------------------------------------------
+# packed blocks
+# ----------------------------------------------------------------------------------------------
+class PRes:
+    """ResBlock (upstream openaimodel.py).  ``emb_col`` = this block's column offset in the
+    per-net batched time-embedding projection (all ``emb_layers.1`` of a net run as ONE GEMM)."""
+
+    def __init__(self, rb, device):
+        self.cin, self.cout = rb.channels, rb.out_channels
+        self.n1 = pack_norm(rb.in_layers[0], device)
+        self.c1 = pack_conv3x3(rb.in_layers[2], device)
+        self.n2 = pack_norm(rb.out_layers[0], device)
+        self.c2 = pack_conv3x3(rb.out_layers[3], device)
+        self.skip = None if isinstance(rb.skip_connection, nn.Identity) else pack_conv1x1(rb.skip_connection, device)
+        self.emb_mod = rb.emb_layers[1]
+        self.emb_col = 0
+
+
+class PAttn:
+    def __init__(self, attn, device):
+        self.heads, self.d = attn.heads, attn.dim_head
+        self.dp = ops.head_pad(self.d)
+        self.hdp = self.heads * self.dp
+        self.scale = self.d ** -0.5
+        self.is_self = attn.context_dim is None
+        kw = dict(heads=self.heads, d=self.d, dp=self.dp)
+        self.q = pack_linear(attn.to_q, device, pad="rows", **kw)
+        self.k = pack_linear(attn.to_k, device, pad="rows", **kw)
+        self.v = pack_linear(attn.to_v, device, pad="rows", **kw)
+        self.o = pack_linear(attn.to_out[0], device, pad="cols", **kw)
+        self.module = attn  # for the optional to_control branch (CrossAttention_LoRA_Control)
+
+
+class PBlock:
+    def __init__(self, blk, device):
+        self.n1, self.n2, self.n3 = (pack_norm(m, device) for m in (blk.norm1, blk.norm2, blk.norm3))
+        self.attn1, self.attn2 = PAttn(blk.attn1, device), PAttn(blk.attn2, device)
+        self.ff0 = pack_geglu(blk.ff.net[0].proj, device)
+        self.ff2 = pack_linear(blk.ff.net[2], device)
+
+
+class PST:
+    def __init__(self, st, device):
+        self.norm = pack_norm(st.norm, device)
+        self.proj_in = pack_conv1x1(st.proj_in, device)
+        self.blocks = [PBlock(b, device) for b in st.transformer_blocks]
+        self.proj_out = pack_conv1x1(st.proj_out, device)
+
+
+class PDown:
+    def __init__(self, m, device):
+        self.conv = pack_conv3x3(m.op, device)  # [Cout, 9C] tap-major, consumed after im2col (stride 2)
+
+
+class PUp:
+    def __init__(self, m, device):
+        self.conv = pack_conv3x3(m.conv, device)
+
+
+class PConvIn:
+    def __init__(self, conv, device):
+        self.w = ops.conv_direct_weight(conv.weight.detach().to(device))
+        self.b = _dev(conv.bias, device, torch.float32)
+        self.cin, self.cout, self.k, self.stride = conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0]
+
+
+def _pack_layer(m, device):
+    from . import ldm
+    if isinstance(m, ldm.ResBlock):
+        return PRes(m, device)
+    if isinstance(m, ldm.SpatialTransformer):
+        return PST(m, device)
+    if isinstance(m, ldm.Downsample):
+        return PDown(m, device)
+    if isinstance(m, ldm.Upsample):
+        return PUp(m, device)
+    if isinstance(m, nn.Conv2d):
+        return PConvIn(m, device)
+    raise capi.TopoError(f"engine: unsupported layer {type(m).__name__}")
+
+
+class PNet:
+    """Packed UNet or ControlNet: time MLP, block lists, and the batched ResBlock time-embedding projection."""
+
+    def __init__(self, net, device, control: bool):
+        self.mc = net.model_channels
+        self.t0 = pack_linear(net.time_embed[0], device)
+        self.t2 = pack_linear(net.time_embed[2], device)
+        self.input_blocks = [[_pack_layer(m, device) for m in blk] for blk in net.input_blocks]
+        self.middle = [_pack_layer(m, device) for m in net.middle_block]
+        self.output_blocks = [] if control else [[_pack_layer(m, device) for m in blk] for blk in net.output_blocks]
+        res = [l for blk in self.input_blocks + [self.middle] + self.output_blocks for l in blk if isinstance(l, PRes)]
+        Ws, bs, col = [], [], 0
+        for r in res:
+            r.emb_col = col
+            Ws.append(r.emb_mod.weight.detach().to(device))
+            bs.append(r.emb_mod.bias.detach().to(device))
+            col += r.cout
+        self.emb_all = Lin(torch.cat(Ws).to(BF16).contiguous(), torch.cat(bs).float().contiguous())
+        if control:
+            self.zero = [pack_conv1x1(z[0], device) for z in net.zero_convs]
+            self.mid_out = pack_conv1x1(net.middle_block_out[0], device)
+            hb = [m for m in net.input_hint_block if isinstance(m, nn.Conv2d)]
+            self.hint = [PConvIn(c, device) for c in hb]
+        else:
+            self.out_norm = pack_norm(net.out[0], device)
+            self.out_conv = pack_conv3x3(net.out[2], device)
+
+    def sts(self) -> List[PST]:
+        return [l for blk in self.input_blocks + [self.middle] + self.output_blocks for l in blk if isinstance(l, PST)]
+
+
+# ----------------------------------------------------------------------------------------------
+# block forwards.  ``dst = (buffer, col)`` makes the block's LAST kernel write its result into a column slice
+# of ``buffer`` (a decoder concat buffer); the function then returns ``buffer``.
+# ----------------------------------------------------------------------------------------------
+Dst = Optional[Tuple[torch.Tensor, int]]
+
+
+def run_res(r: PRes, x: torch.Tensor, B: int, H: int, W: int, emb: torch.Tensor, dst: Dst = None) -> torch.Tensor:
+    rb = emb[:, r.emb_col:r.emb_col + r.cout]
+    h = gn(x, B, r.n1, True)
+    h = conv3(h, B, H, W, r.c1, rowbias=rb)            # + Linear(SiLU(emb))[:, :, None, None] in the epilogue
+    h = gn(h, B, r.n2, True)
+    sk = x if r.skip is None else gemm(x, r.skip)
+    out, col = dst if dst is not None else (None, 0)
+    return conv3(h, B, H, W, r.c2, out=out, out_col=col, res=sk)  # + skip(x) in the epilogue
+
+
+def run_attn(a: PAttn, n: torch.Tensor, h: torch.Tensor, B: int, kv) -> torch.Tensor:
+    """h + to_out(softmax(q k^T d^-1/2) v); ``n`` = LayerNorm(h).  kv None → self-attention (fused q/k/v launch)."""
+    M = n.shape[0]
+    N = M // B
+    hdp = a.hdp
+    if kv is None:
+        qkv = torch.empty(M, 3 * hdp, dtype=BF16, device=n.device)
+        gemm_multi(n, [a.q, a.k, a.v], qkv, [0, hdp, 2 * hdp])
+        t = qkv.view(B, N, 3 * hdp)
+        q, k, v = t[:, :, :hdp], t[:, :, hdp:2 * hdp], t[:, :, 2 * hdp:]
+    else:
+        q = gemm(n, a.q).view(B, N, hdp)
+        k, v = kv
+    o = ops.attention(q, k, v, a.heads, a.dp, a.scale)
+    _count()
+    out = gemm(o.view(M, hdp), a.o, res=h)
+    if getattr(a.module, "control_states", None) is not None:  # CrossAttention_LoRA_Control (attention_lora.py:73-81)
+        out = ops.control_branch(a.module, n.view(B, N, -1), 1.0, add_to=out.view(B, N, -1)).reshape(M, -1)
+        _count(2)
+    return out
+
+
+def run_block(b: PBlock, h: torch.Tensor, B: int, kv) -> torch.Tensor:
+    h = run_attn(b.attn1, ln(h, b.n1), h, B, None)
+    h = run_attn(b.attn2, ln(h, b.n2), h, B, kv)
+    g = gemm(ln(h, b.n3), b.ff0, act=ACT_GEGLU)
+    return gemm(g, b.ff2, res=h)
+
+
+def run_st(st: PST, x: torch.Tensor, B: int, kvs, dst: Dst = None) -> torch.Tensor:
+    h = gemm(gn(x, B, st.norm, False), st.proj_in)
+    for blk, kv in zip(st.blocks, kvs):
+        h = run_block(blk, h, B, kv)
+    out, col = dst if dst is not None else (None, 0)
+    return gemm(h, st.proj_out, out=out, out_col=col, res=x)
+
+
+def run_down(d: PDown, x: torch.Tensor, B: int, H: int, W: int, dst: Dst = None) -> torch.Tensor:
+    cols = ops.im2col3x3_s2(x.view(B, H, W, -1))
+    _count()
+    out, col = dst if dst is not None else (None, 0)
+    return gemm(cols, d.conv, out=out, out_col=col)
+
+
+def run_up(u: PUp, x: torch.Tensor, B: int, H: int, W: int, dst: Dst = None) -> torch.Tensor:
+    y = ops.upsample2x(x.view(B, H, W, -1))
+    _count()
+    out, col = dst if dst is not None else (None, 0)
+    return conv3(y.view(B * 4 * H * W, -1), B, 2 * H, 2 * W, u.conv, out=out, out_col=col)
+
+
+def run_convin(c: PConvIn, x4: torch.Tensor, act: int = ACT_NONE, add: Optional[torch.Tensor] = None,
+               out_fp32: bool = False) -> torch.Tensor:
+    _count()
+    return ops.conv_direct(x4, c.w, c.b, c.cin, c.cout, c.k, c.stride, act=act, add=add, out_fp32=out_fp32)
+
+
+def run_layers(layers, h: torch.Tensor, B: int, H: int, W: int, emb, kv_iter, dst: Dst = None):
+    for i, l in enumerate(layers):
+        d = dst if i == len(layers) - 1 else None
+        if isinstance(l, PRes):
+            h = run_res(l, h, B, H, W, emb, d)
+        elif isinstance(l, PST):
+            h = run_st(l, h, B, next(kv_iter), d)
+        elif isinstance(l, PDown):
+            h = run_down(l, h, B, H, W, d)
+            H, W = H // 2, W // 2
+        elif isinstance(l, PUp):
+            h = run_up(l, h, B, H, W, d)
+            H, W = 2 * H, 2 * W
+        else:
+            raise capi.TopoError(f"engine: unexpected layer {type(l).__name__}")
+    return h, H, W
+
+
+def _block_out_channels(layers) -> int:
+    return [l.cout for l in layers if isinstance(l, PRes)][-1]
+
+
+@dataclass
+class Prepared:
+    """Step-invariant work of one sampling run (hoisted out of the DDIM loop): cross-attention K/V of every
+    transformer block for this context, and the ControlNet hint-block feature map for this hint."""
+    ctx_key: Tuple
+    unet_kv: list
+    cnet_kv: list
+    hint_feat: Optional[torch.Tensor]
+
+
+def fingerprint(model: nn.Module) -> Tuple:
+    """Changes whenever weights are written in place (load_state_dict bumps ``_version``) or modules are swapped."""
+    nv = np_ = 0
+    dev = None
+    for p in model.parameters():
+        nv += p._version
+        np_ += 1
+        dev = p.device
+    return (np_, nv, sum(1 for _ in model.modules()), str(dev), getattr(model, "_topo_surgery_epoch", 0))
+
+
+class TopoEngine:
+    def __init__(self, model):
+        dev = next(model.parameters()).device
+        if dev.type != "cuda":
+            raise capi.TopoError(
+                "TopoEngine: the model is on %s; move it to a B200 (`model.to('cuda')`). There is no CPU forward in "
+                "this package (the fp32 checker lives in oracle/ and is test infrastructure)." % dev)
+        capi.handle(dev.index if dev.index is not None else torch.cuda.current_device())
+        self.device = dev
+        self.fp = fingerprint(model)
+        self.scale_factor = float(model.scale_factor)
+        with torch.no_grad():
+            self.unet = PNet(model.model.diffusion_model, dev, control=False)
+            self.cnet = PNet(model.control_model, dev, control=True)
+            self.vae = None if model.first_stage_model is None else PVae(model.first_stage_model, dev, self.scale_factor)
+
+    def stale(self, model) -> bool:
+        return fingerprint(model) != self.fp
+
+    # ---- step-invariant work -----------------------------------------------------------------
+    def _kv(self, net: PNet, ctx2: torch.Tensor, Be: int):
+        out = []
+        for st in net.sts():
+            per = []
+            for blk in st.blocks:
+                a = blk.attn2
+                kv = torch.empty(ctx2.shape[0], 2 * a.hdp, dtype=BF16, device=ctx2.device)
+                gemm_multi(ctx2, [a.k, a.v], kv, [0, a.hdp])
+                t = kv.view(Be, -1, 2 * a.hdp)
+                per.append((t[:, :, :a.hdp], t[:, :, a.hdp:]))
+            out.append(per)
+        return out
+
+    def _hint(self, hint: torch.Tensor) -> torch.Tensor:
+        """input_hint_block: 8 convs with SiLU between → [Be, H/8, W/8, mc] bf16."""
+        g = ops.nchw_to_nhwc(hint)
+        _count()
+        convs = self.cnet.hint
+        for i, c in enumerate(convs):
+            g = run_convin(c, g, act=ACT_SILU if i != len(convs) - 1 else ACT_NONE)
+        return g
+
+    @torch.no_grad()
+    def prepare(self, ctx: torch.Tensor, hint: Optional[torch.Tensor]) -> Prepared:
+        Be = ctx.shape[0]
+        ctx2 = ctx.reshape(-1, ctx.shape[-1]).to(BF16).contiguous()
+        key = (ctx.data_ptr(), tuple(ctx.shape), None if hint is None else (hint.data_ptr(), tuple(hint.shape)))
+        return Prepared(key, self._kv(self.unet, ctx2, Be), self._kv(self.cnet, ctx2, Be),
+                        None if hint is None else self._hint(hint))
+
+    def _time(self, net: PNet, t: torch.Tensor) -> torch.Tensor:
+        e = ops.timestep_embedding(t, net.mc)
+        e = gemm(e, net.t0, act=ACT_SILU)
+        e = gemm(e, net.t2, act=ACT_SILU)             # SiLU(emb): every ResBlock starts its emb_layers with SiLU
+        _count()
+        return gemm(e, net.emb_all, out_fp32=True)    # all ResBlock Linear(1280→Cout) in one GEMM, fp32 [Be, ΣCout]
+
+    # ---- the hot path --------------------------------------------------------------------------
+    @torch.no_grad()
+    def apply_model(self, x: torch.Tensor, t: torch.Tensor, ctx: torch.Tensor, hint: Optional[torch.Tensor],
+                    control_scales: Sequence[float], only_mid_control: bool = False,
+                    prepared: Optional[Prepared] = None) -> torch.Tensor:
+        """eps [Be,4,H,W] fp32 = UNet(x, t, ctx, control = scales * ControlNet(x, hint, t, ctx))  (SURVEY.md u1-u3)."""
+        if not x.is_cuda:
+            raise capi.TopoError("apply_model: x must be a CUDA tensor (no CPU fallback)")
+        P = prepared if prepared is not None else self.prepare(ctx, hint)
+        Be, _, H0, W0 = x.shape
+        tf = t.to(device=x.device, dtype=torch.float32).contiguous()
+        U, Cn = self.unet, self.cnet
+        x4 = ops.nchw_to_nhwc(x)
+        _count()
+
+        # -- UNet encoder + middle
+        emb = self._time(U, tf)
+        kv = iter(P.unet_kv)
+        h = run_convin(U.input_blocks[0][0], x4).view(Be * H0 * W0, -1)
+        H, W = H0, W0
+        hs, dims = [h], [(H, W)]
+        for blk in U.input_blocks[1:]:
+            h, H, W = run_layers(blk, h, Be, H, W, emb, kv)
+            hs.append(h)
+            dims.append((H, W))
+        h_mid, Hm, Wm = run_layers(U.middle, h, Be, H, W, emb, kv)
+
+        # -- decoder concat buffers [h | skip]; the skip halves are filled by the ControlNet zero-conv epilogues
+        nb = len(U.output_blocks)
+        ch_in = [h_mid.shape[1]] + [_block_out_channels(b) for b in U.output_blocks[:-1]]
+        cat = [torch.empty(hs[nb - 1 - j].shape[0], ch_in[j] + hs[nb - 1 - j].shape[1], dtype=BF16, device=x.device)
+               for j in range(nb)]
+
+        use_control = P.hint_feat is not None
+        if use_control:
+            embc = self._time(Cn, tf)
+            kvc = iter(P.cnet_kv)
+            hc = run_convin(Cn.input_blocks[0][0], x4, add=P.hint_feat).view(Be * H0 * W0, -1)
+            H, W = H0, W0
+            for i, blk in enumerate(Cn.input_blocks):
+                if i:
+                    hc, H, W = run_layers(blk, hc, Be, H, W, embc, kvc)
+                j = nb - 1 - i
+                if only_mid_control:
+                    cat[j][:, ch_in[j]:].copy_(hs[i])
+                else:  # (e) skip + scale*zero_conv(hc) straight into the skip half of concat buffer j
+                    gemm(hc, Cn.zero[i], out=cat[j], out_col=ch_in[j], res=hs[i], alpha=float(control_scales[i]))
+            hc, H, W = run_layers(Cn.middle, hc, Be, H, W, embc, kvc)
+            gemm(hc, Cn.mid_out, out=cat[0], out_col=0, res=h_mid, alpha=float(control_scales[len(Cn.zero)]))
+        else:
+            for j in range(nb):
+                cat[j][:, ch_in[j]:].copy_(hs[nb - 1 - j])
+            cat[0][:, :ch_in[0]].copy_(h_mid)
+
+        # -- UNet decoder: block j reads cat[j] and writes the h half of cat[j+1]
+        H, W = Hm, Wm
+        h = cat[0]
+        for j, blk in enumerate(U.output_blocks):
+            dst = (cat[j + 1], 0) if j + 1 < nb else None
+            h, H, W = run_layers(blk, h, Be, H, W, emb, kv, dst)
+        h = gn(h, Be, U.out_norm, True)
+        e = conv3(h, Be, H, W, U.out_conv, out_fp32=True)
+        _count()
+        return ops.nhwc_to_nchw(e.view(Be, H, W, -1))
+
+    @torch.no_grad()
+    def decode_first_stage(self, z: torch.Tensor) -> torch.Tensor:
+        if self.vae is None:
+            raise capi.TopoError("decode_first_stage: model was built with with_vae=False")
+        return self.vae.decode(z)
+
+
+# ----------------------------------------------------------------------------------------------
+# VAE decoder (AutoencoderKL.decode)
+# ----------------------------------------------------------------------------------------------
+class PVRes:
+    def __init__(self, rb, device):
+        self.n1, self.c1 = pack_norm(rb.norm1, device), pack_conv3x3(rb.conv1, device)
+        self.n2, self.c2 = pack_norm(rb.norm2, device), pack_conv3x3(rb.conv2, device)
+        self.nin = pack_conv1x1(rb.nin_shortcut, device) if hasattr(rb, "nin_shortcut") else None
+
+    def run(self, x, B, H, W):
+        h = conv3(gn(x, B, self.n1, True), B, H, W, self.c1)
+        h = gn(h, B, self.n2, True)
+        sk = x if self.nin is None else gemm(x, self.nin)
+        return conv3(h, B, H, W, self.c2, res=sk)
+
+
+class PVAttn:
+    """Single-head attention over H*W tokens with d = C (512): scores are materialised per tile
+    (S = q k^T as a GEMM, row softmax, P v as a GEMM against v^T); the v bias is added after P·v, which is
+    exact because softmax rows sum to one."""
+
+    def __init__(self, at, device):
+        self.norm = pack_norm(at.norm, device)
+        self.q, self.k = pack_conv1x1(at.q, device), pack_conv1x1(at.k, device)
+        v = pack_conv1x1(at.v, device)
+        self.vW, self.vb = v.W, v.bias
+        self.proj = pack_conv1x1(at.proj_out, device)
+        self.C = self.vW.shape[0]
+
+    def run(self, x, B, H, W):
+        N, C = H * W, self.C
+        hn = gn(x, B, self.norm, False)
+        q, k = gemm(hn, self.q), gemm(hn, self.k)
+        o = torch.empty(B * N, C, dtype=BF16, device=x.device)
+        for b in range(B):
+            sl = slice(b * N, (b + 1) * N)
+            vT = gemm(self.vW, Lin(hn[sl], None))                       # [C, N] = Wv hn^T  (v without bias, transposed)
+            s = gemm(q[sl], Lin(k[sl], None))                           # [N, N]
+            p = ops.softmax_rows(s, C ** -0.5)
+            _count()
+            gemm(p, Lin(vT, self.vb), out=o[sl])
+        return gemm(o, self.proj, res=x)
+
+
+class PVae:
+    def __init__(self, vae, device, scale_factor: float):
+        dec = vae.decoder
+        pq = vae.post_quant_conv
+        # z / scale_factor folded into post_quant_conv: W (z/s) + b = (W/s) z + b
+        w = pq.weight.detach().to(device).float() / scale_factor
+        self.pq_w, self.pq_b = ops.conv_direct_weight(w), _dev(pq.bias, device, torch.float32)
+        self.zc = pq.in_channels
+        self.conv_in = PConvIn(dec.conv_in, device)
+        self.mid1, self.attn, self.mid2 = PVRes(dec.mid.block_1, device), PVAttn(dec.mid.attn_1, device), PVRes(dec.mid.block_2, device)
+        self.levels = []
+        for lvl in reversed(list(dec.up)):
+            blocks = [PVRes(b, device) for b in lvl.block]
+            up = pack_conv3x3(lvl.upsample.conv, device) if hasattr(lvl, "upsample") else None
+            self.levels.append((blocks, up))
+        self.norm_out = pack_norm(dec.norm_out, device)
+        self.conv_out = PConvIn(dec.conv_out, device)
+
+    def decode(self, z: torch.Tensor) -> torch.Tensor:
+        B, _, H, W = z.shape
+        h = ops.nchw_to_nhwc(z.float())
+        h = ops.conv_direct(h, self.pq_w, self.pq_b, self.zc, self.zc, 1, 1)
+        h = run_convin(self.conv_in, h)
+        _count(2)
+        h = h.view(B * H * W, -1)
+        h = self.mid1.run(h, B, H, W)
+        h = self.attn.run(h, B, H, W)
+        h = self.mid2.run(h, B, H, W)
+        for blocks, up in self.levels:
+            for rb in blocks:
+                h = rb.run(h, B, H, W)
+            if up is not None:
+                y = ops.upsample2x(h.view(B, H, W, -1))
+                _count()
+                H, W = 2 * H, 2 * W
+                h = conv3(y.view(B * H * W, -1), B, H, W, up)
+        h = gn(h, B, self.norm_out, True)
+        img = run_convin(self.conv_out, h.view(B, H, W, -1), out_fp32=True)
+        _count()
+        return ops.nhwc_to_nchw(img)

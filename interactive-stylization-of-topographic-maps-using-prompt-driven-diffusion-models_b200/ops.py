@@ -355,3 +355,29 @@ def cross_attention_module(attn, x: torch.Tensor, context: Optional[torch.Tensor
     Ap = None if A is None else pad_head_cols(A, h, d, dp)
     y = linear(o.reshape(Bn * Nq, h * dp), Wp, b, Ap, Bm, s)
     return y.reshape(Bn, Nq, -1).to(x.dtype)
+
+
+def control_branch(attn, hidden: torch.Tensor, scale: float = 1.0, add_to: Optional[torch.Tensor] = None):
+    """``scale * to_control(control_states)`` of CrossAttention_LoRA_Control (LoRA_modified/attention_lora.py:61-80)
+    as two skinny GEMMs (rank zero-padded to one 64-wide K block); with ``add_to`` the sum is fused into the second
+    GEMM's residual epilogue and only applied when the shapes agree, as the reference does (:77-80)."""
+    c = attn.control_states
+    _cuda(c, "to_control")
+    if c.ndim == 4 and hidden.ndim == 3:
+        Bn, Cc, H, Wd = c.shape
+        c = nchw_to_nhwc(c).reshape(Bn, H * Wd, Cc)
+    down, up = attn.to_control[0].weight, attn.to_control[1].weight  # [rc, C], [C, rc]
+    rc, Cc = down.shape
+    kp = ((rc + 63) // 64) * 64
+    dpad = torch.zeros(kp, Cc, dtype=BF16, device=c.device)
+    dpad[:rc] = down.to(BF16)
+    upad = torch.zeros(up.shape[0], kp, dtype=BF16, device=c.device)
+    upad[:, :rc] = up.to(BF16)
+    x2 = c.reshape(-1, Cc).to(BF16).contiguous()
+    t = linear(x2, dpad)
+    out_shape = (*c.shape[:-1], up.shape[0])
+    if add_to is not None and tuple(add_to.shape) != out_shape:
+        return add_to
+    res = None if add_to is None else add_to.reshape(-1, up.shape[0]).to(BF16).contiguous()
+    y = linear(t, upad, res=res, alpha=scale)
+    return y.reshape(out_shape).to(hidden.dtype)
