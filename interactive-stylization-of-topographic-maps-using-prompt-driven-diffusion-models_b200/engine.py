@@ -38,6 +38,39 @@ def _count(n: int = 1) -> None:
     LAUNCHES[0] += n
 
 
+class _Prof:
+    """Optional per-launch CUDA-event bracketing (bench.py's roofline leg): records (kind, flops, bytes, ev0, ev1)
+    for the tensor-core / attention / norm launches on the stream they are launched on."""
+    on = False
+    recs: list = []
+
+
+PROF = _Prof()
+
+
+def _rec(kind: str, flops: float, nbytes: float, fn):
+    if not PROF.on:
+        return fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    r = fn()
+    e1.record()
+    PROF.recs.append((kind, flops, nbytes, e0, e1))
+    return r
+
+
+def prof_summary() -> Dict[str, Dict[str, float]]:
+    """kind -> {launches, ms, flops, bytes}; call after torch.cuda.synchronize()."""
+    out: Dict[str, Dict[str, float]] = {}
+    for kind, fl, nb, e0, e1 in PROF.recs:
+        d = out.setdefault(kind, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
+        d["launches"] += 1
+        d["ms"] += e0.elapsed_time(e1)
+        d["flops"] += fl
+        d["bytes"] += nb
+    return out
+
+
 # ----------------------------------------------------------------------------------------------
 # packed weights
 # ----------------------------------------------------------------------------------------------
@@ -50,6 +83,7 @@ class Lin:
     B: Optional[torch.Tensor] = None      # bf16 [N, rp]
     rp: int = 0
     s: float = 1.0
+    r: int = 0                            # true LoRA rank (algorithmic FLOPs are counted on r, not on the padded rp)
 
     @property
     def N(self) -> int:
@@ -80,10 +114,11 @@ def pack_linear(mod: nn.Module, device, heads: int = 0, d: int = 0, dp: int = 0,
     elif pad == "cols" and dp != d:
         W = ops.pad_head_cols(W, heads, d, dp)
         A = None if A is None else ops.pad_head_cols(A, heads, d, dp)
-    rp = 0
+    rp = r = 0
     if A is not None:
+        r = A.shape[0]
         A, Bm, rp = ops.prep_lora(A, Bm)
-    return Lin(W.to(BF16).contiguous(), _dev(b, device, torch.float32), A, Bm, rp, s)
+    return Lin(W.to(BF16).contiguous(), _dev(b, device, torch.float32), A, Bm, rp, s, r)
 
 
 def pack_conv1x1(conv: nn.Conv2d, device) -> Lin:
@@ -137,7 +172,9 @@ def gemm(x: torch.Tensor, lin: Lin, out: Optional[torch.Tensor] = None, out_col:
                       out_ld=out.stride(0), out_col=out_col, out_fp32=out_fp32, res=res,
                       res_ld=0 if res is None else res.stride(0), res_col=res_col, rowbias=rowbias,
                       rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=rows_per_group, act=act)
-    ops.lora_linear_raw(x, M, lin.K, x.stride(0), [seg])
+    fl = 2.0 * M * lin.N * lin.K + 2.0 * M * lin.r * (lin.K + lin.N)
+    _rec("gemm_lora" if lin.r else "gemm", fl, 2.0 * (M * lin.K + lin.N * lin.K + M * n_out),
+         lambda: ops.lora_linear_raw(x, M, lin.K, x.stride(0), [seg]))
     _count()
     return out
 
@@ -148,7 +185,11 @@ def gemm_multi(x: torch.Tensor, lins: Sequence[Lin], out: torch.Tensor, cols: Se
     if len({l.rp for l in lins}) == 1 and len({l.K for l in lins}) == 1 and len(lins) <= 3:
         segs = [make_linear(l.W, out, l.N, bias=l.bias, A=l.A, B=l.B, r_pad=l.rp, s=l.s, out_ld=out.stride(0),
                             out_col=c) for l, c in zip(lins, cols)]
-        ops.lora_linear_raw(x, M, lins[0].K, x.stride(0), segs)
+        K = lins[0].K
+        fl = sum(2.0 * M * l.N * K + 2.0 * M * l.r * (K + l.N) for l in lins)
+        nb = 2.0 * (M * K + sum(l.N * K + M * l.N for l in lins))
+        _rec("gemm_lora" if any(l.r for l in lins) else "gemm", fl, nb,
+             lambda: ops.lora_linear_raw(x, M, K, x.stride(0), segs))
         _count()
     else:
         for l, c in zip(lins, cols):
@@ -165,20 +206,23 @@ def conv3(x: torch.Tensor, B: int, H: int, W: int, lin: Lin, out: Optional[torch
     seg = make_linear(lin.W, out, lin.N, bias=lin.bias, out_ld=out.stride(0), out_col=out_col, out_fp32=out_fp32,
                       res=res, res_ld=0 if res is None else res.stride(0), res_col=res_col, rowbias=rowbias,
                       rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=H * W)
-    ops.conv3x3_raw(x, B, H, W, C, x.stride(0), seg)
+    M = B * H * W
+    _rec("conv3x3", 2.0 * M * lin.N * 9 * C, 2.0 * (M * C + lin.N * 9 * C + M * lin.N),
+         lambda: ops.conv3x3_raw(x, B, H, W, C, x.stride(0), seg))
     _count()
     return out
 
 
 def gn(x: torch.Tensor, B: int, n: Norm, silu: bool) -> torch.Tensor:
-    y = ops.groupnorm_silu(x.view(B, -1, x.shape[1]), n.gamma, n.beta, n.groups, n.eps, silu)
+    y = _rec("groupnorm_silu", 0.0, 4.0 * x.numel(),
+             lambda: ops.groupnorm_silu(x.view(B, -1, x.shape[1]), n.gamma, n.beta, n.groups, n.eps, silu))
     _count(2)
     return y.view(x.shape)
 
 
 def ln(x: torch.Tensor, n: Norm) -> torch.Tensor:
     _count()
-    return ops.layernorm(x, n.gamma, n.beta, n.eps)
+    return _rec("layernorm", 0.0, 4.0 * x.numel(), lambda: ops.layernorm(x, n.gamma, n.beta, n.eps))
 
 
 # ----------------------------------------------------------------------------------------------
@@ -323,7 +367,9 @@ def run_attn(a: PAttn, n: torch.Tensor, h: torch.Tensor, B: int, kv) -> torch.Te
     else:
         q = gemm(n, a.q).view(B, N, hdp)
         k, v = kv
-    o = ops.attention(q, k, v, a.heads, a.dp, a.scale)
+    Nk = k.shape[1]
+    o = _rec("attn_self" if kv is None else "attn_cross", 4.0 * B * a.heads * N * Nk * a.d,
+             2.0 * (2 * M * hdp + 2 * B * Nk * hdp), lambda: ops.attention(q, k, v, a.heads, a.dp, a.scale))
     _count()
     out = gemm(o.view(M, hdp), a.o, res=h)
     if getattr(a.module, "control_states", None) is not None:  # CrossAttention_LoRA_Control (attention_lora.py:73-81)
@@ -538,6 +584,13 @@ class TopoEngine:
             raise capi.TopoError("decode_first_stage: model was built with with_vae=False")
         return self.vae.decode(z)
 
+    @torch.no_grad()
+    def decode_to_u8(self, z: torch.Tensor) -> torch.Tensor:
+        """decode_first_stage + uint8 HWC conversion on the device → [B, 8H, 8W, 3] uint8."""
+        if self.vae is None:
+            raise capi.TopoError("decode_to_u8: model was built with with_vae=False")
+        return self.vae.decode(z, u8=True)
+
 
 # ----------------------------------------------------------------------------------------------
 # VAE decoder (AutoencoderKL.decode; SURVEY.md A.5, row N2)
@@ -601,7 +654,7 @@ class PVae:
         self.norm_out = pack_norm(dec.norm_out, device)
         self.conv_out = PConvIn(dec.conv_out, device)
 
-    def decode(self, z: torch.Tensor) -> torch.Tensor:
+    def decode(self, z: torch.Tensor, u8: bool = False) -> torch.Tensor:
         B, _, H, W = z.shape
         h = ops.nchw_to_nhwc(z.float())
         h = ops.conv_direct(h, self.pq_w, self.pq_b, self.zc, self.zc, 1, 1)
@@ -622,4 +675,69 @@ class PVae:
         h = gn(h, B, self.norm_out, True)
         img = run_convin(self.conv_out, h.view(B, H, W, -1), out_fp32=True)
         _count()
+        if u8:  # evaluateCN.py:101-103: *127.5+127.5, clip, truncate → uint8 HWC, fused before the gather
+            return ops.tile_to_u8(img)
         return ops.nhwc_to_nchw(img)
+
+
+# ----------------------------------------------------------------------------------------------
+# CUDA-graph replay (one apply_model = ~550 launches; captured once per shape, replayed per DDIM step)
+# ----------------------------------------------------------------------------------------------
+class GraphedModel:
+    """Static-buffer CUDA graphs of ``prepare`` (per tile batch) and ``apply_model`` (per DDIM step).
+
+    ``t`` lives in a device buffer read by the timestep-embedding kernel, so ONE step graph serves every timestep.
+    The kernels are captured on torch's capture stream through the C ABI's ``stream`` argument; TMA descriptors are
+    encoded on the host at capture time and baked into the graph as kernel parameters."""
+
+    def __init__(self, eng: TopoEngine, Be: int, lat_hw: Tuple[int, int], ctx_shape: Tuple[int, int],
+                 hint_hw: Optional[Tuple[int, int]], control_scales: Sequence[float], only_mid_control: bool):
+        dev = eng.device
+        self.eng = eng
+        self.x = torch.zeros(Be, 4, *lat_hw, device=dev)
+        self.t = torch.zeros(Be, device=dev)
+        self.ctx = torch.zeros(Be, *ctx_shape, device=dev)
+        self.hint = None if hint_hw is None else torch.zeros(Be, 3, *hint_hw, device=dev)
+        scales = [float(s) for s in control_scales]
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):  # warm-up outside capture: function attributes, workspaces, lazy inits
+            P = eng.prepare(self.ctx, self.hint)
+            eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=P)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        n0 = LAUNCHES[0]
+        self.g_prep = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_prep):
+            self.P = eng.prepare(self.ctx, self.hint)
+        self.prep_launches = LAUNCHES[0] - n0
+        n0 = LAUNCHES[0]
+        self.g_step = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_step, pool=self.g_prep.pool()):
+            self.eps = eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=self.P)
+        self.step_launches = LAUNCHES[0] - n0
+
+    def set_cond(self, ctx: torch.Tensor, hint: Optional[torch.Tensor]) -> None:
+        self.ctx.copy_(ctx, non_blocking=True)
+        if self.hint is not None:
+            self.hint.copy_(hint, non_blocking=True)
+        self.g_prep.replay()
+        _count(self.prep_launches)
+
+    def step(self) -> torch.Tensor:
+        """Replay apply_model on the current contents of ``self.x`` / ``self.t``; returns the static eps buffer."""
+        self.g_step.replay()
+        _count(self.step_launches)
+        return self.eps
+
+
+def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control) -> GraphedModel:
+    key = (Be, tuple(lat_hw), tuple(ctx_shape), None if hint_hw is None else tuple(hint_hw),
+           tuple(float(s) for s in control_scales), bool(only_mid_control))
+    cache = self.__dict__.setdefault("_graphs", {})
+    if key not in cache:
+        cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control)
+    return cache[key]
+
+
+TopoEngine.graphed = _graphed

@@ -14,6 +14,7 @@ import numpy as np
 import torch
 
 from . import capi, ops
+from .engine import GraphedModel
 
 
 def make_ddim_timesteps(S: int, T: int = 1000) -> np.ndarray:
@@ -66,36 +67,49 @@ class DDIMSampler:
         w = float(unconditional_guidance_scale)
 
         def _pack(cond):
-            ctx = torch.cat(cond["c_crossattn"], 1).to(dev)
+            ctx = torch.cat(cond["c_crossattn"], 1).to(dev, torch.float32)
             hint = None if cond.get("c_concat") is None else torch.cat(cond["c_concat"], 1).to(dev, torch.float32)
             return ctx, hint
 
         if cfg and not self.hacked:
-            ctx, hint = _pack(self._cat_cond(unconditional_conditioning, conditioning))
-            plans = [(ctx, hint, eng.prepare(ctx, hint))]
+            conds = [_pack(self._cat_cond(unconditional_conditioning, conditioning))]
         elif cfg:
-            plans = []
-            for cnd in (unconditional_conditioning, conditioning):  # eps buffer layout is [uncond ; cond]
-                ctx, hint = _pack(cnd)
-                plans.append((ctx, hint, eng.prepare(ctx, hint)))
+            conds = [_pack(unconditional_conditioning), _pack(conditioning)]  # eps buffer layout is [uncond ; cond]
         else:
-            ctx, hint = _pack(conditioning)
-            plans = [(ctx, hint, eng.prepare(ctx, hint))]
+            conds = [_pack(conditioning)]
+        scales, omc = model.control_scales, model.only_mid_control
+        rep = conds[0][0].shape[0] // batch_size      # 2 when the CFG pair is batched into one call
+        use_graph = bool(getattr(model, "use_cuda_graphs", True))
+        if use_graph:
+            runs = []
+            for ctx, hint in conds:
+                # the hacked variant needs two sets of static buffers: distinct graphs for the two branches
+                g = eng.graphed(ctx.shape[0], (H, W), tuple(ctx.shape[1:]), None if hint is None else tuple(hint.shape[2:]),
+                                scales, omc) if len(conds) == 1 else GraphedModel(
+                                    eng, ctx.shape[0], (H, W), tuple(ctx.shape[1:]),
+                                    None if hint is None else tuple(hint.shape[2:]), scales, omc)
+                g.set_cond(ctx, hint)
+                runs.append(g)
+        else:
+            plans = [(ctx, hint, eng.prepare(ctx, hint)) for ctx, hint in conds]
 
         inter = {"x_inter": [img], "pred_x0": []}
         ts = self.ddim_timesteps
         n = len(ts)
-        scales, omc = model.control_scales, model.only_mid_control
         for i in reversed(range(n)):
-            t = torch.full((batch_size,), int(ts[i]), device=dev, dtype=torch.long)
-            if cfg and not self.hacked:
-                ctx, hint, P = plans[0]
-                eps = eng.apply_model(torch.cat([img, img]), torch.cat([t, t]), ctx, hint, scales, omc, prepared=P)
-            elif cfg:
-                eps = torch.cat([eng.apply_model(img, t, c_, h_, scales, omc, prepared=P) for c_, h_, P in plans])
+            if use_graph:
+                outs = []
+                for g in runs:
+                    for r in range(rep):
+                        g.x[r * batch_size:(r + 1) * batch_size].copy_(img)
+                    g.t.fill_(float(ts[i]))
+                    outs.append(g.step())
+                eps = outs[0] if len(outs) == 1 else torch.cat(outs)
             else:
-                ctx, hint, P = plans[0]
-                eps = eng.apply_model(img, t, ctx, hint, scales, omc, prepared=P)
+                t = torch.full((batch_size * rep,), int(ts[i]), device=dev, dtype=torch.long)
+                xin = img if rep == 1 else torch.cat([img] * rep)
+                outs = [eng.apply_model(xin, t, c_, h_, scales, omc, prepared=P) for c_, h_, P in plans]
+                eps = outs[0] if len(outs) == 1 else torch.cat(outs)
             sig = float(self.ddim_sigmas[i])
             noise = torch.randn_like(img) if sig != 0.0 else None  # sigma = 0 (eta = 0) on every reference call
             img = ops.ddim_step(img, eps, cfg, w, float(self.ddim_alphas[i]), float(self.ddim_alphas_prev[i]), sig, noise)
