@@ -57,7 +57,8 @@ struct GemmSmem {
   static constexpr int LB_BYTES = BN * RPAD * 2;
   static constexpr int T_BYTES = BM * RPAD * 2;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES + LB_BYTES + T_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;  // barriers + alignment slack
+  static constexpr int TOTAL = BAR_OFF + 256 + 512 + 1024;  // barriers + bias tile + alignment slack
+  static_assert(STAGES * STAGE_BYTES >= BM * BN * 4, "epilogue staging tile must fit in the pipeline stages");
 };
 
 template <int BN, int RPAD, int STAGES, bool CONV>
@@ -225,87 +226,101 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       tc_fence_before();
       mbar_arrive(t_ready);
     }
+    // bias tile -> smem while the main loop runs (one coalesced load instead of 128 broadcast loads per thread)
+    float* sbias = reinterpret_cast<float*>(smem + L::BAR_OFF + 256);
+    {
+      const int n = n0 + (threadIdx.x - 64);
+      sbias[threadIdx.x - 64] = (sg.bias && n < sg.N) ? __ldg(sg.bias + n) : 0.f;
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     mbar_wait(final_full, 0);
     tc_fence_after();
 
+    // ---- phase A: one accumulator row per thread.  TMEM -> registers, bias / per-sample bias / activation / alpha,
+    //      then fp32 into a staging tile that reuses the (now dead) pipeline stages: [128 rows][NC cols], 16-byte
+    //      units XOR-swizzled with (row & 7) so both the row-per-thread writes and the row-per-warp reads below are
+    //      bank-conflict free.
     const int m = m0 + row;
     const bool row_ok = m < p.M;
     const bool geglu = sg.act == TOPO_ACT_GEGLU;
-    const int ncols_tile = geglu ? BN / 2 : BN;         // accumulator columns that produce outputs
+    const int NC = geglu ? BN / 2 : BN;                 // output columns this tile produces
     const int out_n0 = geglu ? n0 / 2 : n0;             // first output column of this tile
     const int out_N = geglu ? sg.N / 2 : sg.N;
     const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
-    const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 7) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 7) == 0);
-
+    float* stage = reinterpret_cast<float*>(smem);
+    float* srow = stage + (size_t)row * NC;
+    const int rsw = row & 7;
 #pragma unroll 1
-    for (int c = 0; c < ncols_tile / 32; ++c) {
+    for (int c = 0; c < NC / 32; ++c) {
       float v[32];
       tmem_ld32(tmem_acc + lane_addr + c * 32, v);
-      float g[32];
-      if (geglu) tmem_ld32(tmem_acc + lane_addr + BN / 2 + c * 32, g);
-      tmem_ld_wait();
-      const int nb = out_n0 + c * 32;  // first output column of this chunk
-      if (row_ok && nb < out_N) {
+      if (geglu) {
+        float g[32];
+        tmem_ld32(tmem_acc + lane_addr + BN / 2 + c * 32, g);
+        tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int n = nb + j;
-        if (n < out_N) {
-          float x = v[j];
-          if (geglu) {
-            // accumulator column of a: n0 + c*32 + j ; gate: n0 + BN/2 + c*32 + j (same for bias)
-            const int na = n0 + c * 32 + j, ng = na + BN / 2;
-            float gg = g[j];
-            if (sg.bias) {
-              x += __ldg(sg.bias + na);
-              gg += __ldg(sg.bias + ng);
-            }
-            x = x * gelu_erf_f(gg);
-          } else {
-            if (sg.bias) x += __ldg(sg.bias + n);
-            if (rb) x += __ldg(rb + n);
-            if (sg.act == TOPO_ACT_SILU) x = silu_f(x);
-          }
+        for (int j = 0; j < 32; ++j) {
+          const float a = v[j] + sbias[c * 32 + j];
+          const float gg = g[j] + sbias[BN / 2 + c * 32 + j];
+          v[j] = a * gelu_erf_f(gg) * sg.alpha;
+        }
+      } else {
+        tmem_ld_wait();
+        const int nb = out_n0 + c * 32;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = v[j] + sbias[c * 32 + j];
+          if (rb && nb + j < out_N) x += __ldg(rb + nb + j);
+          if (sg.act == TOPO_ACT_SILU) x = silu_f(x);
           v[j] = x * sg.alpha;
         }
       }
-      if (vec_ok) {
 #pragma unroll
-        for (int j8 = 0; j8 < 4; ++j8) {
-          const int n = nb + j8 * 8;
-          if (n >= out_N) break;
-          float* w = v + j8 * 8;
-          if (sg.res) {
-            const uint4 r = __ldg(reinterpret_cast<const uint4*>(sg.res + (size_t)m * sg.res_ld + sg.res_col + n));
-            w[0] += bf16lo(r.x); w[1] += bf16hi(r.x); w[2] += bf16lo(r.y); w[3] += bf16hi(r.y);
-            w[4] += bf16lo(r.z); w[5] += bf16hi(r.z); w[6] += bf16lo(r.w); w[7] += bf16hi(r.w);
-          }
-          if (sg.out_fp32) {
-            float* o = reinterpret_cast<float*>(sg.out) + (size_t)m * sg.out_ld + sg.out_col + n;
-            *reinterpret_cast<float4*>(o) = make_float4(w[0], w[1], w[2], w[3]);
-            *reinterpret_cast<float4*>(o + 4) = make_float4(w[4], w[5], w[6], w[7]);
-          } else {
-            bf16* o = reinterpret_cast<bf16*>(sg.out) + (size_t)m * sg.out_ld + sg.out_col + n;
-            uint4 u;
-            u.x = pack_bf16x2(w[0], w[1]); u.y = pack_bf16x2(w[2], w[3]);
-            u.z = pack_bf16x2(w[4], w[5]); u.w = pack_bf16x2(w[6], w[7]);
-            *reinterpret_cast<uint4*>(o) = u;
-          }
+      for (int u = 0; u < 8; ++u)
+        *reinterpret_cast<float4*>(srow + (((c * 8 + u) ^ rsw) << 2)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+    }
+    __syncwarp();
+
+    // ---- phase B: each warp streams ITS 32 rows out, a full row (or two half rows) per instruction: lanes run along
+    //      the columns, so residual loads and output stores are contiguous 8/16-byte pieces of one 256/512-byte line.
+    const int lpr = NC / 4;                  // lanes per row (32 or 16)
+    const int rpi = 32 / lpr;                // rows per iteration (1 or 2)
+    const int unit = lane % lpr;
+    const int n = out_n0 + unit * 4;
+    const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
+#pragma unroll 1
+    for (int it = 0; it < 32 / rpi; ++it) {
+      const int r = q * 32 + it * rpi + lane / lpr;
+      const int mm = m0 + r;
+      if (mm >= p.M || n >= out_N) continue;
+      const float4 f = *reinterpret_cast<const float4*>(stage + (size_t)r * NC + ((unit ^ (r & 7)) << 2));
+      float w[4] = {f.x, f.y, f.z, f.w};
+      if (vec_ok) {
+        if (sg.res) {
+          const uint2 rr = __ldg(reinterpret_cast<const uint2*>(sg.res + (size_t)mm * sg.res_ld + sg.res_col + n));
+          w[0] += bf16lo(rr.x); w[1] += bf16hi(rr.x); w[2] += bf16lo(rr.y); w[3] += bf16hi(rr.y);
+        }
+        if (sg.out_fp32) {
+          *reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) =
+              make_float4(w[0], w[1], w[2], w[3]);
+        } else {
+          uint2 o;
+          o.x = pack_bf16x2(w[0], w[1]);
+          o.y = pack_bf16x2(w[2], w[3]);
+          *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) = o;
         }
       } else {
-        for (int j = 0; j < 32; ++j) {
-          const int n = nb + j;
-          if (n >= out_N) break;
-          float x = v[j];
-          if (sg.res) x += __bfloat162float(sg.res[(size_t)m * sg.res_ld + sg.res_col + n]);
+        for (int j = 0; j < 4 && n + j < out_N; ++j) {
+          float x = w[j];
+          if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
           if (sg.out_fp32)
-            reinterpret_cast<float*>(sg.out)[(size_t)m * sg.out_ld + sg.out_col + n] = x;
+            reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
           else
-            reinterpret_cast<bf16*>(sg.out)[(size_t)m * sg.out_ld + sg.out_col + n] = __float2bfloat16(x);
+            reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
         }
       }
-      }
-      __syncwarp();  // reconverge before the next warp-collective tcgen05.ld
     }
+    __syncwarp();
     tc_fence_before();
   }
 

@@ -20,6 +20,9 @@ __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
 }
 
 // grid (splits, B). Block handles pixels [split*ppb, min(HW, (split+1)*ppb)) of sample b.
+// Thread -> FIXED channel vector (so sums stay in registers): the block is cut into `rows` pixel lanes of `vpr`
+// threads (rows = 256 / vpr; threads beyond rows*vpr idle); for vpr > 256 the channel range is walked in chunks.
+// 4 independent 16-byte loads in flight per thread.
 __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __restrict__ x, int x_ld, int HW, int C, int G,
                                                              int ppb, float* __restrict__ ws) {
   extern __shared__ float sh[];  // [2*C] per-channel sum, sumsq
@@ -32,39 +35,43 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
   const int p0 = split * ppb;
   const int p1 = min(HW, p0 + ppb);
   const bf16* xb = x + (size_t)b * HW * x_ld;
-  // thread -> fixed channel vector when possible (vpr divides the stride), generic otherwise
-  const int total = (p1 - p0) * vpr;
-  if (GN_THREADS % vpr == 0) {
-    const int v = threadIdx.x % vpr;
-    const int prow = threadIdx.x / vpr, pstep = GN_THREADS / vpr;
-    float s[8], q[8];
+  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;   // threads across the channel dimension
+  const int rows = GN_THREADS / lanes;                     // pixel rows processed in parallel
+  const int prow = threadIdx.x / lanes;
+  if (prow < rows) {
+    for (int v = threadIdx.x % lanes; v < vpr; v += lanes) {
+      float s[8], q[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
-    for (int pp = p0 + prow; pp < p1; pp += pstep) {
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
-      float f[8];
-      unpack8(u, f);
+      for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+      int pp = p0 + prow;
+      for (; pp + 3 * rows < p1; pp += 4 * rows) {
+        uint4 u[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        s[i] += f[i];
-        q[i] = fmaf(f[i], f[i], q[i]);
+        for (int k = 0; k < 4; ++k) u[k] = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)(pp + k * rows) * x_ld) + v);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float f[8];
+          unpack8(u[k], f);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            s[i] += f[i];
+            q[i] = fmaf(f[i], f[i], q[i]);
+          }
+        }
       }
-    }
+      for (; pp < p1; pp += rows) {
+        float f[8];
+        unpack8(__ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v), f);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      atomicAdd(&ch_sum[v * 8 + i], s[i]);
-      atomicAdd(&ch_sq[v * 8 + i], q[i]);
-    }
-  } else {
-    for (int idx = threadIdx.x; idx < total; idx += GN_THREADS) {
-      const int pp = p0 + idx / vpr, v = idx % vpr;
-      const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
-      float f[8];
-      unpack8(u, f);
+        for (int i = 0; i < 8; ++i) {
+          s[i] += f[i];
+          q[i] = fmaf(f[i], f[i], q[i]);
+        }
+      }
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        atomicAdd(&ch_sum[v * 8 + i], f[i]);
-        atomicAdd(&ch_sq[v * 8 + i], f[i] * f[i]);
+        atomicAdd(&ch_sum[v * 8 + i], s[i]);
+        atomicAdd(&ch_sq[v * 8 + i], q[i]);
       }
     }
   }
@@ -118,23 +125,41 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const bf16* __rest
   const int vpr = C >> 3;
   const int p0 = blockIdx.x * ppb;
   const int p1 = min(HW, p0 + ppb);
-  const int total = (p1 - p0) * vpr;
   const bf16* xb = x + (size_t)b * HW * x_ld;
   bf16* yb = y + (size_t)b * HW * y_ld;
-  for (int idx = threadIdx.x; idx < total; idx += GN_THREADS) {
-    const int pp = p0 + idx / vpr, v = idx % vpr;
-    const uint4 u = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v);
-    float f[8];
-    unpack8(u, f);
+  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;
+  const int rows = GN_THREADS / lanes;
+  const int prow = threadIdx.x / lanes;
+  if (prow >= rows) return;
+  for (int v = threadIdx.x % lanes; v < vpr; v += lanes) {
+    float a[8], c[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float t = fmaf(f[i], sc[v * 8 + i], sf[v * 8 + i]);
-      f[i] = apply_silu ? silu_f(t) : t;
+      a[i] = sc[v * 8 + i];
+      c[i] = sf[v * 8 + i];
     }
-    uint4 o;
-    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-    *(reinterpret_cast<uint4*>(yb + (size_t)pp * y_ld) + v) = o;
+    auto emit = [&](const uint4& u, int pp) {
+      float f[8];
+      unpack8(u, f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float t = fmaf(f[i], a[i], c[i]);
+        f[i] = apply_silu ? __fdividef(t, 1.0f + __expf(-t)) : t;
+      }
+      uint4 o;
+      o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+      o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+      *(reinterpret_cast<uint4*>(yb + (size_t)pp * y_ld) + v) = o;
+    };
+    int pp = p0 + prow;
+    for (; pp + 3 * rows < p1; pp += 4 * rows) {
+      uint4 u[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) u[k] = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)(pp + k * rows) * x_ld) + v);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) emit(u[k], pp + k * rows);
+    }
+    for (; pp < p1; pp += rows) emit(__ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v), pp);
   }
 }
 
