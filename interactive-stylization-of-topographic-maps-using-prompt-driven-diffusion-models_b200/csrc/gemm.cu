@@ -288,35 +288,47 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     const int unit = lane % lpr;
     const int n = out_n0 + unit * 4;
     const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
+    constexpr int UB = 8;  // row-iterations in flight: all smem + residual loads are issued before the first store
 #pragma unroll 1
-    for (int it = 0; it < 32 / rpi; ++it) {
-      const int r = q * 32 + it * rpi + lane / lpr;
-      const int mm = m0 + r;
-      if (mm >= p.M || n >= out_N) continue;
-      const float4 f = *reinterpret_cast<const float4*>(stage + (size_t)r * NC + ((unit ^ (r & 7)) << 2));
-      float w[4] = {f.x, f.y, f.z, f.w};
-      if (vec_ok) {
-        if (sg.res) {
-          const uint2 rr = __ldg(reinterpret_cast<const uint2*>(sg.res + (size_t)mm * sg.res_ld + sg.res_col + n));
-          w[0] += bf16lo(rr.x); w[1] += bf16hi(rr.x); w[2] += bf16lo(rr.y); w[3] += bf16hi(rr.y);
-        }
-        if (sg.out_fp32) {
-          *reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) =
-              make_float4(w[0], w[1], w[2], w[3]);
+    for (int it0 = 0; it0 < 32 / rpi; it0 += UB) {
+      float4 f[UB];
+      uint2 rr[UB];
+      bool ok[UB];
+#pragma unroll
+      for (int k = 0; k < UB; ++k) {
+        const int r = q * 32 + (it0 + k) * rpi + lane / lpr;
+        const int mm = m0 + r;
+        ok[k] = mm < p.M && n < out_N;
+        f[k] = *reinterpret_cast<const float4*>(stage + (size_t)r * NC + ((unit ^ (r & 7)) << 2));
+        rr[k] = make_uint2(0u, 0u);
+        if (vec_ok && sg.res && ok[k])
+          rr[k] = __ldg(reinterpret_cast<const uint2*>(sg.res + (size_t)mm * sg.res_ld + sg.res_col + n));
+      }
+#pragma unroll
+      for (int k = 0; k < UB; ++k) {
+        if (!ok[k]) continue;
+        const int mm = m0 + q * 32 + (it0 + k) * rpi + lane / lpr;
+        float w[4] = {f[k].x, f[k].y, f[k].z, f[k].w};
+        if (vec_ok) {
+          w[0] += bf16lo(rr[k].x); w[1] += bf16hi(rr[k].x); w[2] += bf16lo(rr[k].y); w[3] += bf16hi(rr[k].y);
+          if (sg.out_fp32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) =
+                make_float4(w[0], w[1], w[2], w[3]);
+          } else {
+            uint2 o;
+            o.x = pack_bf16x2(w[0], w[1]);
+            o.y = pack_bf16x2(w[2], w[3]);
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) = o;
+          }
         } else {
-          uint2 o;
-          o.x = pack_bf16x2(w[0], w[1]);
-          o.y = pack_bf16x2(w[2], w[3]);
-          *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) = o;
-        }
-      } else {
-        for (int j = 0; j < 4 && n + j < out_N; ++j) {
-          float x = w[j];
-          if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
-          if (sg.out_fp32)
-            reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
-          else
-            reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
+          for (int j = 0; j < 4 && n + j < out_N; ++j) {
+            float x = w[j];
+            if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
+            if (sg.out_fp32)
+              reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
+            else
+              reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
+          }
         }
       }
     }
