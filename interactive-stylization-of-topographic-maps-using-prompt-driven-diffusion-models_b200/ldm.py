@@ -506,17 +506,18 @@ def create_model(config="stock", **overrides) -> ControlLDM:
         unet_surgery = None
     else:
         name = str(config)
-        for key in VARIANTS:  # accept the reference's yaml file names too
-            if key.lower() in name.lower():
-                name = key
-        if "rank12" in name:
-            v = dict(control_lora_rank=12, unet=None)
-        elif "rank32" in name:
-            v = dict(control_lora_rank=32, unet=None)
+        import re
+        m = re.search(r"rank(\d+)", name)
+        if m:  # the reference's yaml names: ctrlora_finetune_sd15_rank12.yaml / …rank32.yaml (…_ctrlora.py:216, …_addlrSD.py:281)
+            v = dict(control_lora_rank=int(m.group(1)), unet=None)
         elif "cldm_v15" in name:
             v = VARIANTS["stock"]
         else:
-            v = VARIANTS[name]
+            hit = [key for key in VARIANTS if key.lower() == name.lower()] or \
+                  [key for key in VARIANTS if key.lower() in name.lower()]
+            if not hit:
+                raise KeyError(f"unknown model config {config!r}; variants: {sorted(VARIANTS)}")
+            v = VARIANTS[hit[0]]
         cfg = ModelConfig(control_lora_rank=v["control_lora_rank"])
         unet_surgery = v["unet"]
     for k, val in overrides.items():
