@@ -38,7 +38,7 @@ int topo_version(void);
 /* activation selectors for topo_linear_t.act */
 #define TOPO_ACT_NONE 0
 #define TOPO_ACT_SILU 1
-#define TOPO_ACT_GEGLU 2 /* columns of W are tile-interleaved [64 x a | 64 x gate] per 128; output has N/2 columns */
+#define TOPO_ACT_GEGLU 2 /* rows of W are tile-interleaved [t/2 values | t/2 gates] per t = topo_geglu_tile(N) rows; output has N/2 columns */
 
 /* One output segment of a projection:   out = alpha * (x W^T + s (x A^T) B^T + bias + rowbias) + res
  * Replaces LoRALinear.forward (LoRA_modified/LoRA_utils.py:40-42), the ctrlora lora_layer branch
@@ -68,6 +68,8 @@ typedef struct {
 /* (a) fused projection: n_seg (1..3) segments share one read of x [M, K] (row stride x_ld elements).
  *     n_seg = 3 is the fused q/k/v projection of CrossAttention.forward (upstream ldm attention.py;
  *     LoRA wrapped per LoRA_modified/LoRA_utils.py:45-59).                                          */
+/* N-tile width (128 or 256) the GEGLU epilogue pairs value/gate columns over, for a projection with N output rows. */
+int topo_geglu_tile(int N);
 int topo_lora_linear(topo_handle_t h, const void* x, int M, int K, int x_ld, const topo_linear_t* segs, int n_seg,
                      void* stream);
 

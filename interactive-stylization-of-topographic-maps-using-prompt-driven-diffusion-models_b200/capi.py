@@ -23,7 +23,7 @@ SYMBOLS = [
     "topo_attention", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
     "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_conv_direct",
     "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2",
-    "topo_add_bf16", "topo_tile_to_u8", "topo_softmax_rows",
+    "topo_add_bf16", "topo_tile_to_u8", "topo_softmax_rows", "topo_geglu_tile",
 ]
 
 
@@ -67,6 +67,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_attention.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]
     lib.topo_groupnorm_silu.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp, vp]
     lib.topo_groupnorm_ws_floats.argtypes = [i32, i32]
+    lib.topo_geglu_tile.argtypes = [i32]
     lib.topo_layernorm.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, f32, vp]
     lib.topo_zeroconv_residual.argtypes = [vp, vp, i32, vp, vp, f32, vp, i32, vp, i32, i32, i32, i32, vp]
     lib.topo_timestep_embedding.argtypes = [vp, vp, vp, i32, i32, vp]

@@ -76,6 +76,7 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
                        int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t st);
 int groupnorm_ws_floats(int B, int G);
+int gemm_geglu_tile(int N);
 int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int B, int HW,
                        int C, int G, float eps, int apply_silu, float* ws, cudaStream_t st);
 int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int M, int C,
@@ -188,6 +189,7 @@ int topo_attention(topo_handle_t h, const void* q, const void* k, const void* v,
 }
 
 int topo_groupnorm_ws_floats(int B, int G) { return groupnorm_ws_floats(B, G); }
+int topo_geglu_tile(int N) { return gemm_geglu_tile(N); }
 
 int topo_groupnorm_silu(topo_handle_t h, const void* x, int x_ld, const float* gamma, const float* beta, void* y,
                         int y_ld, int B, int HW, int C, int G, float eps, int apply_silu, float* ws, void* stream) {

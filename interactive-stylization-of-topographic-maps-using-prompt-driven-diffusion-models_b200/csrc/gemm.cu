@@ -1,19 +1,23 @@
-// K1/K5/K6/K7/K9 — the projection GEMM family of the hot path, one warp-specialised tcgen05 kernel:
+// K1/K5/K6/K7/K9 — the projection GEMM family of the hot path, one PERSISTENT warp-specialised tcgen05 kernel:
 //
 //   out = alpha * ( x W^T  +  s (x A^T) B^T  + bias + rowbias ) + res          (optionally SiLU / GEGLU)
 //
-//  * x tile   : TMA -> smem (SWIZZLE_128B, K-major), 2-D rows or a 4-D NHWC box shifted per filter tap
-//               (implicit-GEMM 3x3 conv; TMA out-of-bounds zero fill is the conv padding)
-//  * W tile   : TMA -> smem, K-major;  UMMA M=128, N=BN, K=16 per instruction, fp32 accumulator in TMEM
-//  * LoRA     : the SAME x tile also feeds a side UMMA  T = x A^T (N = r_pad) into a second TMEM region;
-//               after the K loop the epilogue warps move s*T (bf16) TMEM->smem, and ONE more UMMA adds
-//               T B^T into the main accumulator — the low-rank delta never touches HBM.
-//  * epilogue : TMEM -> registers (tcgen05.ld 32x32b), bias / per-sample bias / activation / residual, 16 B stores
-//               to an arbitrary (ld, column offset) destination, so q/k/v, concat buffers and the ControlNet
-//               zero-conv residual are written in place.
-//  warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = epilogue (TMEM lane quadrant = warp & 3).
-//  Two CTAs are co-resident per SM (<= 113 KB smem, <= 256 TMEM columns each) so one CTA's epilogue
-//  overlaps the other's main loop.
+//  * one CTA per SM walks a static tile list (tile = blockIdx.x + i * gridDim.x); three pipelines run concurrently:
+//      warp 0      TMA producer   : x / W / LoRA-A tiles -> 4-stage smem ring (SWIZZLE_128B, K-major); x is a 2-D row
+//                                   tile or a 4-D NHWC box shifted per filter tap (implicit-GEMM 3x3 conv; TMA
+//                                   out-of-bounds zero fill is the conv padding).  Runs ahead across tile boundaries.
+//      warp 1      MMA issuer     : UMMA M=128, N=BN, K=16 into one of TWO fp32 accumulators in TMEM, so the epilogue
+//                                   of tile i overlaps the main loop of tile i+1
+//      warps 2..9  epilogue       : TMEM -> registers (tcgen05.ld 32x32b; two warps per TMEM lane quadrant, each half of
+//                                   the columns), bias / per-sample bias / activation, fp32 staging tile in smem
+//                                   (XOR-swizzled 16-byte units), then row-contiguous residual loads + stores to an
+//                                   arbitrary (ld, column offset) destination: q/k/v, concat buffers and the ControlNet
+//                                   zero-conv residual are written in place.
+//  * LoRA: the SAME x tile also feeds a side UMMA  T = x A^T (N = r_pad) into a third TMEM region; after the K loop
+//    the epilogue warps move s*T (bf16) TMEM->smem and ONE more UMMA adds T B^T into the main accumulator — the
+//    low-rank delta never touches HBM.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "topo_b200.h"
 
@@ -21,7 +25,9 @@ namespace topo {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int EPI_WARPS = 8;
+constexpr int EPI_THREADS = EPI_WARPS * 32;
+constexpr int GEMM_THREADS = 64 + EPI_THREADS;
 constexpr int MAX_SEG = 3;
 
 struct alignas(64) GemmSegDev {
@@ -36,7 +42,7 @@ struct alignas(64) GemmSegDev {
   int res_ld, res_col, rowbias_ld, rows_per_group;
   int act;
   float s, alpha;
-  int pad_;
+  int n_tiles;        // ceil(N / BN)
 };
 
 struct alignas(64) GemmParams {
@@ -44,6 +50,7 @@ struct alignas(64) GemmParams {
   GemmSegDev seg[MAX_SEG];
   int M, K;          // K = channels per tap
   int taps;          // 1 or 9
+  int n_seg, m_tiles, total_tiles;
   // conv geometry
   int H, W, bw, bh, bb, tiles_w, tiles_h;
 };
@@ -56,68 +63,100 @@ struct GemmSmem {
   static constexpr int STAGE_BYTES = A_BYTES + W_BYTES + LA_BYTES;
   static constexpr int LB_BYTES = BN * RPAD * 2;
   static constexpr int T_BYTES = BM * RPAD * 2;
-  static constexpr int BAR_OFF = STAGES * STAGE_BYTES + LB_BYTES + T_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 512 + 1024;  // barriers + bias tile + alignment slack
-  static_assert(STAGES * STAGE_BYTES >= BM * BN * 4, "epilogue staging tile must fit in the pipeline stages");
+  static constexpr int LB_OFF = STAGES * STAGE_BYTES;
+  static constexpr int T_OFF = LB_OFF + LB_BYTES;
+  static constexpr int STG_OFF = T_OFF + T_BYTES;          // fp32 staging: [32 rows][32 cols] per epilogue warp
+  static constexpr int BIAS_OFF = STG_OFF + EPI_WARPS * 32 * 32 * 4;   // 2 x BN floats
+  static constexpr int BAR_OFF = BIAS_OFF + 2 * BN * 4;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;       // barriers + alignment slack
+  static_assert(TOTAL <= 232448, "shared memory budget exceeded");
 };
+
+struct TileCoord {
+  int seg, n0, m0, cw0, ch0, cb0;
+};
+
+// tile id -> (segment, n tile, m tile); m fastest so concurrently running CTAs share one W tile and stream x.
+template <int BN, bool CONV>
+__device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
+  TileCoord c;
+  int sgi = 0, rem = tile;
+#pragma unroll
+  for (int i = 0; i < MAX_SEG - 1; ++i) {
+    const int cnt = p.seg[i].n_tiles * p.m_tiles;
+    if (sgi == i && i + 1 < p.n_seg && rem >= cnt) {
+      rem -= cnt;
+      sgi = i + 1;
+    }
+  }
+  c.seg = sgi;
+  const int nt = rem / p.m_tiles, mt = rem - nt * p.m_tiles;
+  c.n0 = nt * BN;
+  c.cw0 = c.ch0 = c.cb0 = 0;
+  if (CONV) {
+    int t = mt;
+    const int tw = t % p.tiles_w;
+    t /= p.tiles_w;
+    const int th = t % p.tiles_h;
+    const int tb = t / p.tiles_h;
+    c.cw0 = tw * p.bw;
+    c.ch0 = th * p.bh;
+    c.cb0 = tb * p.bb;
+    c.m0 = (c.cb0 * p.H + c.ch0) * p.W + c.cw0;
+  } else {
+    c.m0 = mt * BM;
+  }
+  return c;
+}
 
 template <int BN, int RPAD, int STAGES, bool CONV>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
   using L = GemmSmem<BN, RPAD, STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* lb_tile = smem + STAGES * L::STAGE_BYTES;
-  uint8_t* t_tile = lb_tile + L::LB_BYTES;
+  uint8_t* lb_tile = smem + L::LB_OFF;
+  uint8_t* t_tile = smem + L::T_OFF;
+  float* stage_f = reinterpret_cast<float*>(smem + L::STG_OFF);
+  float* sbias_all = reinterpret_cast<float*>(smem + L::BIAS_OFF);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
-  uint64_t* full = bars;                  // [STAGES]
-  uint64_t* empty = bars + STAGES;        // [STAGES]
-  uint64_t* lb_full = bars + 2 * STAGES;  // LoRA-B tile landed
-  uint64_t* side_full = lb_full + 1;      // main loop (acc + T) finished
-  uint64_t* t_ready = lb_full + 2;        // s*T written to smem by the 128 epilogue threads
-  uint64_t* final_full = lb_full + 3;     // accumulator complete
+  uint64_t* full = bars;                   // [STAGES] TMA landed
+  uint64_t* empty = bars + STAGES;         // [STAGES] MMAs that read the stage finished
+  uint64_t* tfull = bars + 2 * STAGES;     // [2] accumulator complete
+  uint64_t* tempty = tfull + 2;            // [2] accumulator drained by the epilogue (EPI_THREADS arrivals)
+  uint64_t* lb_full = tempty + 2;          // LoRA-B tile landed
+  uint64_t* lb_empty = lb_full + 1;        // LoRA-up MMA finished reading lb_tile / t_tile
+  uint64_t* side_full = lb_full + 2;       // main loop (acc + T) finished
+  uint64_t* t_ready = lb_full + 3;         // s*T written to smem (128 arrivals)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lb_full + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const GemmSegDev& sg = p.seg[blockIdx.z];
-  const int n0 = blockIdx.y * BN;
-  if (n0 >= sg.N) return;  // segment narrower than the widest one of this launch (CTA-uniform)
   const int kc = p.K / BK;
   const int num_kb = p.taps * kc;
-
-  // tile origin
-  int m0, cw0 = 0, ch0 = 0, cb0 = 0;
-  if (CONV) {
-    int t = blockIdx.x;
-    const int tw = t % p.tiles_w;
-    t /= p.tiles_w;
-    const int th = t % p.tiles_h;
-    const int tb = t / p.tiles_h;
-    cw0 = tw * p.bw;
-    ch0 = th * p.bh;
-    cb0 = tb * p.bb;
-    m0 = (cb0 * p.H + ch0) * p.W + cw0;
-  } else {
-    m0 = blockIdx.x * BM;
-  }
-
-  constexpr uint32_t TMEM_COLS = (BN + RPAD) <= 32 ? 32 : (BN + RPAD) <= 64 ? 64 : (BN + RPAD) <= 128 ? 128 : 256;
+  constexpr uint32_t TMEM_COLS = 512;
+  constexpr uint32_t T_COL = 2 * BN;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tm_x);
-    tma_prefetch_desc(&sg.tm_w);
-    if (RPAD) {
-      tma_prefetch_desc(&sg.tm_la);
-      tma_prefetch_desc(&sg.tm_lb);
+    for (int i = 0; i < p.n_seg; ++i) {
+      tma_prefetch_desc(&p.seg[i].tm_w);
+      if (RPAD) {
+        tma_prefetch_desc(&p.seg[i].tm_la);
+        tma_prefetch_desc(&p.seg[i].tm_lb);
+      }
     }
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full[i], 1);
       mbar_init(&empty[i], 1);
     }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], EPI_THREADS);
+    }
     mbar_init(lb_full, 1);
+    mbar_init(lb_empty, 1);
     mbar_init(side_full, 1);
     mbar_init(t_ready, 128);
-    mbar_init(final_full, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
@@ -125,217 +164,303 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_acc = tmem_base;
-  const uint32_t tmem_t = tmem_base + BN;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      if (RPAD) {
-        mbar_expect_tx(lb_full, L::LB_BYTES);
-        tma_load_2d(lb_tile, &sg.tm_lb, lb_full, 0, n0);
-      }
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&empty[stage], phase ^ 1);
-        uint8_t* a_s = smem + stage * L::STAGE_BYTES;
-        uint8_t* w_s = a_s + L::A_BYTES;
-        uint8_t* la_s = w_s + L::W_BYTES;
-        mbar_expect_tx(&full[stage], L::STAGE_BYTES);
-        if (CONV) {
-          const int tap = kb / kc;
-          const int c0 = (kb - tap * kc) * BK;
-          const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-          tma_load_4d(a_s, &p.tm_x, &full[stage], c0, cw0 + dx, ch0 + dy, cb0);
-        } else {
-          tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, m0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const TileCoord c = tile_coord<BN, CONV>(p, tile);
+        const GemmSegDev& sg = p.seg[c.seg];
+        if (RPAD) {
+          mbar_wait(lb_empty, (it & 1) ^ 1);  // previous tile's LoRA-up MMA is done with lb_tile
+          mbar_expect_tx(lb_full, L::LB_BYTES);
+          tma_load_2d(lb_tile, &sg.tm_lb, lb_full, 0, c.n0);
         }
-        tma_load_2d(w_s, &sg.tm_w, &full[stage], kb * BK, n0);
-        if (RPAD) tma_load_2d(la_s, &sg.tm_la, &full[stage], kb * BK, 0);
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* a_s = smem + stage * L::STAGE_BYTES;
+          uint8_t* w_s = a_s + L::A_BYTES;
+          uint8_t* la_s = w_s + L::W_BYTES;
+          mbar_expect_tx(&full[stage], L::STAGE_BYTES);
+          if (CONV) {
+            const int tap = kb / kc;
+            const int c0 = (kb - tap * kc) * BK;
+            const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+            tma_load_4d(a_s, &p.tm_x, &full[stage], c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
+          } else {
+            tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, c.m0);
+          }
+          tma_load_2d(w_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
+          if (RPAD) tma_load_2d(la_s, &sg.tm_la, &full[stage], kb * BK, 0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc_main = make_idesc_bf16(BM, BN);
       constexpr uint32_t idesc_side = make_idesc_bf16(BM, RPAD ? RPAD : 16);
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full[stage], phase);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t tmem_acc = tmem_base + buf * BN;
+        const uint32_t tmem_t = tmem_base + T_COL;
+        // the last N tile of a segment only multiplies the columns that exist (UMMA N is a run-time field, multiple of 16)
+        const TileCoord c = tile_coord<BN, CONV>(p, tile);
+        const int n_left = p.seg[c.seg].N - c.n0;
+        const uint32_t n_eff = n_left >= BN ? BN : ((n_left + 15) & ~15);
+        const uint32_t idesc_main = make_idesc_bf16(BM, n_eff);
+        mbar_wait(&tempty[buf], ((it >> 1) & 1) ^ 1);  // epilogue drained this accumulator (two tiles ago)
         tc_fence_after();
-        const uint32_t a_s = smem_u32(smem + stage * L::STAGE_BYTES);
-        const uint32_t w_s = a_s + L::A_BYTES;
-        const uint32_t la_s = w_s + L::W_BYTES;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_s = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t w_s = a_s + L::A_BYTES;
+          const uint32_t la_s = w_s + L::W_BYTES;
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
-          umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
-          if (RPAD) umma_bf16(tmem_t, ad, kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
+            umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
+            if (RPAD) umma_bf16(tmem_t, ad, kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
         }
-        umma_commit(&empty[stage]);
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-      if (RPAD) {
-        umma_commit(side_full);
-        mbar_wait(lb_full, 0);
-        mbar_wait(t_ready, 0);
-        tc_fence_after();
-        const uint32_t t_s = smem_u32(t_tile);
-        const uint32_t lb_s = smem_u32(lb_tile);
+        if (RPAD) {
+          umma_commit(side_full);
+          mbar_wait(lb_full, it & 1);
+          mbar_wait(t_ready, it & 1);
+          tc_fence_after();
+          const uint32_t t_s = smem_u32(t_tile);
+          const uint32_t lb_s = smem_u32(lb_tile);
 #pragma unroll
-        for (int k = 0; k < RPAD / 16; ++k)
-          umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, 1);
+          for (int k = 0; k < RPAD / 16; ++k)
+            umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, 1);
+          umma_commit(lb_empty);
+        }
+        umma_commit(&tfull[buf]);
       }
-      umma_commit(final_full);
     }
   } else {
-    // ===================== epilogue (4 warps = 128 accumulator rows) =====================
+    // ===================== epilogue (8 warps; TMEM lane quadrant = warp & 3, column half = (warp - 2) >> 2) =====
     const int q = warp & 3;
+    const int hsel = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64;
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
-    if (RPAD) {
-      mbar_wait(side_full, 0);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      const TileCoord c = tile_coord<BN, CONV>(p, tile);
+      const GemmSegDev& sg = p.seg[c.seg];
+      const int buf = it & 1;
+      const uint32_t tmem_acc = tmem_base + buf * BN;
+      float* sbias = sbias_all + buf * BN;
+      // bias tile -> smem (double-buffered by tile parity; the barrier also orders tile i-1's staging reads
+      // before tile i's staging writes across the two warps that share a row quadrant? no: each warp only touches
+      // its own rows x columns of the staging tile, so __syncwarp suffices for staging; the barrier is for sbias)
+      if (et < BN) {
+        const int n = c.n0 + et;
+        sbias[et] = (sg.bias && n < sg.N) ? __ldg(sg.bias + n) : 0.f;
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
+
+      if (RPAD && hsel == 0) {
+        // s*T (fp32, TMEM) -> bf16 K-major swizzled smem tile, the A operand of the LoRA-up UMMA
+        mbar_wait(side_full, it & 1);
+        tc_fence_after();
+        float t[RPAD ? RPAD : 16];
+        tmem_ld16(tmem_base + T_COL + lane_addr, t);
+        if (RPAD == 32) tmem_ld16(tmem_base + T_COL + lane_addr + 16, t + 16);
+        tmem_ld_wait();
+        constexpr uint32_t span = (RPAD ? RPAD : 16) * 2;
+        constexpr uint32_t mask = span / 16 - 1;
+#pragma unroll
+        for (int j = 0; j < RPAD / 8; ++j) {
+          uint32_t off = row * span + j * 16;
+          off ^= ((off >> 7) & mask) << 4;
+          uint4 v;
+          v.x = pack_bf16x2(t[j * 8 + 0] * sg.s, t[j * 8 + 1] * sg.s);
+          v.y = pack_bf16x2(t[j * 8 + 2] * sg.s, t[j * 8 + 3] * sg.s);
+          v.z = pack_bf16x2(t[j * 8 + 4] * sg.s, t[j * 8 + 5] * sg.s);
+          v.w = pack_bf16x2(t[j * 8 + 6] * sg.s, t[j * 8 + 7] * sg.s);
+          *reinterpret_cast<uint4*>(t_tile + off) = v;
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(t_ready);
+      }
+
+      mbar_wait(&tfull[buf], (it >> 1) & 1);
       tc_fence_after();
-      float t[RPAD ? RPAD : 16];
-      tmem_ld16(tmem_t + lane_addr, t);
-      if (RPAD == 32) tmem_ld16(tmem_t + lane_addr + 16, t + 16);
-      tmem_ld_wait();
-      constexpr uint32_t span = RPAD * 2;
-      constexpr uint32_t mask = span / 16 - 1;
-#pragma unroll
-      for (int j = 0; j < RPAD / 8; ++j) {
-        uint32_t off = row * span + j * 16;
-        off ^= ((off >> 7) & mask) << 4;
-        uint4 v;
-        v.x = pack_bf16x2(t[j * 8 + 0] * sg.s, t[j * 8 + 1] * sg.s);
-        v.y = pack_bf16x2(t[j * 8 + 2] * sg.s, t[j * 8 + 3] * sg.s);
-        v.z = pack_bf16x2(t[j * 8 + 4] * sg.s, t[j * 8 + 5] * sg.s);
-        v.w = pack_bf16x2(t[j * 8 + 6] * sg.s, t[j * 8 + 7] * sg.s);
-        *reinterpret_cast<uint4*>(t_tile + off) = v;
-      }
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(t_ready);
-    }
-    // bias tile -> smem while the main loop runs (one coalesced load instead of 128 broadcast loads per thread)
-    float* sbias = reinterpret_cast<float*>(smem + L::BAR_OFF + 256);
-    {
-      const int n = n0 + (threadIdx.x - 64);
-      sbias[threadIdx.x - 64] = (sg.bias && n < sg.N) ? __ldg(sg.bias + n) : 0.f;
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-    }
-    mbar_wait(final_full, 0);
-    tc_fence_after();
 
-    // ---- phase A: one accumulator row per thread.  TMEM -> registers, bias / per-sample bias / activation / alpha,
-    //      then fp32 into a staging tile that reuses the (now dead) pipeline stages: [128 rows][NC cols], 16-byte
-    //      units XOR-swizzled with (row & 7) so both the row-per-thread writes and the row-per-warp reads below are
-    //      bank-conflict free.
-    const int m = m0 + row;
-    const bool row_ok = m < p.M;
-    const bool geglu = sg.act == TOPO_ACT_GEGLU;
-    const int NC = geglu ? BN / 2 : BN;                 // output columns this tile produces
-    const int out_n0 = geglu ? n0 / 2 : n0;             // first output column of this tile
-    const int out_N = geglu ? sg.N / 2 : sg.N;
-    const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
-    float* stage = reinterpret_cast<float*>(smem);
-    float* srow = stage + (size_t)row * NC;
-    const int rsw = row & 7;
+      // ---- the warp owns rows [q*32, +32) x output columns [hsel*colsw, +colsw) of the tile and walks them in
+      //      32-column chunks: phase A (row per thread: TMEM -> registers -> bias/activation -> fp32 staging, 4 KB per
+      //      warp, 16-byte units XOR-swizzled with row&7) then phase B (8 lanes per row, 4 rows per instruction, all 8
+      //      row-groups in flight: residual loads and stores are full 128-byte lines).  Branches on the tile-uniform
+      //      epilogue flavour are hoisted out of the per-column loops.
+      const int m = c.m0 + row;
+      const bool row_ok = m < p.M;
+      const bool geglu = sg.act == TOPO_ACT_GEGLU;
+      const int NC = geglu ? BN / 2 : BN;        // output columns this tile produces
+      const int out_n0 = geglu ? c.n0 / 2 : c.n0;
+      const int out_N = geglu ? sg.N / 2 : sg.N;
+      const int nchunk = NC / 64;                // 32-column chunks per warp
+      const float alpha = sg.alpha;
+      const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
+      const bool plain = (rb == nullptr) && sg.act == TOPO_ACT_NONE;
+      const bool silu = sg.act == TOPO_ACT_SILU;
+      const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
+      float* wstage = stage_f + (warp - 2) * (32 * 32);     // this warp's [32 rows][32 cols] fp32 staging
+      float* srow = wstage + lane * 32;
+      const int sub = lane >> 3;                 // phase B: row within a 4-row group
+      const int unit = lane & 7;                 // phase B: 16-byte unit (4 columns) within the 32-column chunk
+      const int rows_left = p.M - (c.m0 + q * 32 + sub);
 #pragma unroll 1
-    for (int c = 0; c < NC / 32; ++c) {
-      float v[32];
-      tmem_ld32(tmem_acc + lane_addr + c * 32, v);
-      if (geglu) {
-        float g[32];
-        tmem_ld32(tmem_acc + lane_addr + BN / 2 + c * 32, g);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float a = v[j] + sbias[c * 32 + j];
-          const float gg = g[j] + sbias[BN / 2 + c * 32 + j];
-          v[j] = a * gelu_erf_f(gg) * sg.alpha;
+      for (int ch = 0; ch < nchunk; ++ch) {
+        const int c32 = hsel * nchunk + ch;      // 32-column chunk index among the tile's OUTPUT columns
+        if (out_n0 + c32 * 32 >= out_N) {        // chunk entirely beyond the segment's last column (N tail)
+          if (ch == nchunk - 1) {
+            tc_fence_before();
+            mbar_arrive(&tempty[buf]);
+          }
+          continue;
         }
-      } else {
-        tmem_ld_wait();
-        const int nb = out_n0 + c * 32;
+        float v[32];
+        if (geglu) {
+          float g[32];
+          tmem_ld32(tmem_acc + lane_addr + c32 * 32, v);
+          tmem_ld32(tmem_acc + lane_addr + BN / 2 + c32 * 32, g);
+          tmem_ld_wait();
+          const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32);
+          const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float x = v[j] + sbias[c * 32 + j];
-          if (rb && nb + j < out_N) x += __ldg(rb + nb + j);
-          if (sg.act == TOPO_ACT_SILU) x = silu_f(x);
-          v[j] = x * sg.alpha;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u)
-        *reinterpret_cast<float4*>(srow + (((c * 8 + u) ^ rsw) << 2)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
-    }
-    __syncwarp();
-
-    // ---- phase B: each warp streams ITS 32 rows out, a full row (or two half rows) per instruction: lanes run along
-    //      the columns, so residual loads and output stores are contiguous 8/16-byte pieces of one 256/512-byte line.
-    const int lpr = NC / 4;                  // lanes per row (32 or 16)
-    const int rpi = 32 / lpr;                // rows per iteration (1 or 2)
-    const int unit = lane % lpr;
-    const int n = out_n0 + unit * 4;
-    const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
-    constexpr int UB = 8;  // row-iterations in flight: all smem + residual loads are issued before the first store
-#pragma unroll 1
-    for (int it0 = 0; it0 < 32 / rpi; it0 += UB) {
-      float4 f[UB];
-      uint2 rr[UB];
-      bool ok[UB];
-#pragma unroll
-      for (int k = 0; k < UB; ++k) {
-        const int r = q * 32 + (it0 + k) * rpi + lane / lpr;
-        const int mm = m0 + r;
-        ok[k] = mm < p.M && n < out_N;
-        f[k] = *reinterpret_cast<const float4*>(stage + (size_t)r * NC + ((unit ^ (r & 7)) << 2));
-        rr[k] = make_uint2(0u, 0u);
-        if (vec_ok && sg.res && ok[k])
-          rr[k] = __ldg(reinterpret_cast<const uint2*>(sg.res + (size_t)mm * sg.res_ld + sg.res_col + n));
-      }
-#pragma unroll
-      for (int k = 0; k < UB; ++k) {
-        if (!ok[k]) continue;
-        const int mm = m0 + q * 32 + (it0 + k) * rpi + lane / lpr;
-        float w[4] = {f[k].x, f[k].y, f[k].z, f[k].w};
-        if (vec_ok) {
-          w[0] += bf16lo(rr[k].x); w[1] += bf16hi(rr[k].x); w[2] += bf16lo(rr[k].y); w[3] += bf16hi(rr[k].y);
-          if (sg.out_fp32) {
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) =
-                make_float4(w[0], w[1], w[2], w[3]);
-          } else {
-            uint2 o;
-            o.x = pack_bf16x2(w[0], w[1]);
-            o.y = pack_bf16x2(w[2], w[3]);
-            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(sg.out) + (size_t)mm * sg.out_ld + sg.out_col + n) = o;
+          for (int u = 0; u < 8; ++u) {
+            const float4 a4 = ba[u], g4 = bg[u];
+            v[4 * u + 0] = (v[4 * u + 0] + a4.x) * gelu_erf_f(g[4 * u + 0] + g4.x) * alpha;
+            v[4 * u + 1] = (v[4 * u + 1] + a4.y) * gelu_erf_f(g[4 * u + 1] + g4.y) * alpha;
+            v[4 * u + 2] = (v[4 * u + 2] + a4.z) * gelu_erf_f(g[4 * u + 2] + g4.z) * alpha;
+            v[4 * u + 3] = (v[4 * u + 3] + a4.w) * gelu_erf_f(g[4 * u + 3] + g4.w) * alpha;
           }
         } else {
-          for (int j = 0; j < 4 && n + j < out_N; ++j) {
-            float x = w[j];
-            if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
-            if (sg.out_fp32)
-              reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
-            else
-              reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
+          tmem_ld32(tmem_acc + lane_addr + c32 * 32, v);
+          tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(sbias + c32 * 32);
+          if (plain) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float4 bb = b4[u];
+              v[4 * u] = (v[4 * u] + bb.x) * alpha;
+              v[4 * u + 1] = (v[4 * u + 1] + bb.y) * alpha;
+              v[4 * u + 2] = (v[4 * u + 2] + bb.z) * alpha;
+              v[4 * u + 3] = (v[4 * u + 3] + bb.w) * alpha;
+            }
+          } else {
+            const int nb = out_n0 + c32 * 32;
+            const bool rb_vec = rb && ((reinterpret_cast<uintptr_t>(rb + nb) & 15) == 0) && nb + 32 <= out_N;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const float4 bb = b4[u];
+              float x[4] = {v[4 * u] + bb.x, v[4 * u + 1] + bb.y, v[4 * u + 2] + bb.z, v[4 * u + 3] + bb.w};
+              if (rb_vec) {
+                const float4 r4 = __ldg(reinterpret_cast<const float4*>(rb + nb) + u);
+                x[0] += r4.x; x[1] += r4.y; x[2] += r4.z; x[3] += r4.w;
+              } else if (rb) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  if (nb + 4 * u + j < out_N) x[j] += __ldg(rb + nb + 4 * u + j);
+              }
+              if (silu) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) x[j] = silu_f(x[j]);
+              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j) v[4 * u + j] = x[j] * alpha;
+            }
           }
         }
+        if (ch == nchunk - 1) {
+          tc_fence_before();
+          mbar_arrive(&tempty[buf]);             // accumulator drained: the MMA warp may start tile it+2 into it
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          *reinterpret_cast<float4*>(srow + ((u ^ (lane & 7)) << 2)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+        __syncwarp();
+
+        const int n = out_n0 + c32 * 32 + unit * 4;
+        if (vec_ok) {
+          if (n < out_N) {
+            const bool has_res = sg.res != nullptr;
+            const size_t row0 = (size_t)(c.m0 + q * 32 + sub);
+            const bf16* resp = has_res ? sg.res + row0 * sg.res_ld + sg.res_col + n : nullptr;
+            const size_t res_step = (size_t)4 * sg.res_ld, out_step = (size_t)4 * sg.out_ld;
+            const size_t out_off = row0 * sg.out_ld + sg.out_col + n;
+            float4 f[8];
+            uint2 rr[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const int r = k * 4 + sub;         // row within the warp's 32
+              f[k] = *reinterpret_cast<const float4*>(wstage + r * 32 + ((unit ^ (r & 7)) << 2));
+              rr[k] = make_uint2(0u, 0u);
+              if (has_res && k * 4 < rows_left) rr[k] = __ldg(reinterpret_cast<const uint2*>(resp + k * res_step));
+            }
+            if (sg.out_fp32) {
+              float* op = reinterpret_cast<float*>(sg.out) + out_off;
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (k * 4 < rows_left)
+                  *reinterpret_cast<float4*>(op + k * out_step) =
+                      make_float4(f[k].x + bf16lo(rr[k].x), f[k].y + bf16hi(rr[k].x), f[k].z + bf16lo(rr[k].y), f[k].w + bf16hi(rr[k].y));
+            } else {
+              bf16* op = reinterpret_cast<bf16*>(sg.out) + out_off;
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                if (k * 4 < rows_left) {
+                  uint2 o;
+                  o.x = pack_bf16x2(f[k].x + bf16lo(rr[k].x), f[k].y + bf16hi(rr[k].x));
+                  o.y = pack_bf16x2(f[k].z + bf16lo(rr[k].y), f[k].w + bf16hi(rr[k].y));
+                  *reinterpret_cast<uint2*>(op + k * out_step) = o;
+                }
+            }
+          }
+        } else {
+          // unaligned destinations (rare: N or ld not a multiple of 4): scalar path
+#pragma unroll 1
+          for (int k = 0; k < 8; ++k) {
+            const int r = k * 4 + sub;
+            const int mm = c.m0 + q * 32 + r;
+            if (mm >= p.M) continue;
+            const float4 f = *reinterpret_cast<const float4*>(wstage + r * 32 + ((unit ^ (r & 7)) << 2));
+            const float w[4] = {f.x, f.y, f.z, f.w};
+            for (int j = 0; j < 4 && n + j < out_N; ++j) {
+              float x = w[j];
+              if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
+              if (sg.out_fp32)
+                reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
+              else
+                reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
+            }
+          }
+        }
+        __syncwarp();
       }
+      __syncwarp();
     }
-    __syncwarp();
-    tc_fence_before();
   }
 
+  tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
@@ -349,15 +474,52 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 template <int BN, int RPAD, int STAGES, bool CONV>
 static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
+  static_assert((BN == 128 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad) or 256 (no LoRA)");
   auto kfn = gemm_kernel<BN, RPAD, STAGES, CONV>;
   static bool attr_set = false;
   if (!attr_set) {
     TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set = true;
   }
-  kfn<<<grid, GEMM_THREADS, L::TOTAL, st>>>(p);
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    TOPO_CUDA(cudaGetDevice(&dev));
+    TOPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  (void)grid;
+  const int ctas = p.total_tiles < sms ? p.total_tiles : sms;  // persistent: one CTA per SM walks the tile list
+  kfn<<<ctas, GEMM_THREADS, L::TOTAL, st>>>(p);
   TOPO_CUDA(cudaGetLastError());
   return 0;
+}
+
+// GEGLU column interleave granularity the host must pack with (ops.geglu_interleave): values | gates per N tile.
+int gemm_geglu_tile(int N) { return (N % 256 == 0) ? 256 : 128; }
+
+static int sm_count() {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+  }
+  return sms;
+}
+
+// 256-wide N tiles cut L2->SM operand traffic per FLOP by 25% and halve the number of MMA instructions; they need
+// enough tiles to keep every SM busy for at least two rounds.  TOPO_BN=128|256 overrides (experiments).
+static int pick_bn(int m_tiles, int N, int r_pad, int n_seg, int act) {
+  if (r_pad != 0 || n_seg != 1) return 128;
+  if (act == TOPO_ACT_GEGLU) return gemm_geglu_tile(N);
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("TOPO_BN");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 128 || forced == 256) return forced;
+  if (N < 256) return 128;
+  const int tiles256 = m_tiles * ((N + 255) / 256);
+  return tiles256 >= 2 * sm_count() ? 256 : 128;
 }
 
 static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int BN) {
@@ -397,6 +559,7 @@ static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int 
   d.act = s.act;
   d.s = s.s;
   d.alpha = s.alpha;
+  d.n_tiles = (s.N + BN - 1) / BN;
   return 0;
 }
 
@@ -405,7 +568,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   TOPO_CHECK(K % BK == 0 && K > 0, TOPO_E_INVAL, "K (%d) must be a positive multiple of 64", K);
   TOPO_CHECK(x_ld % 8 == 0, TOPO_E_INVAL, "x_ld must be a multiple of 8 elements");
   TOPO_CHECK(M > 0, TOPO_E_INVAL, "M must be positive");
-  constexpr int BN = 128;
+  const int BN = pick_bn((M + BM - 1) / BM, segs[0].N, segs[0].r_pad, n_seg, segs[0].act);
   GemmParams p;
   memset(&p, 0, sizeof(p));
   uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -423,17 +586,23 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   p.M = M;
   p.K = K;
   p.taps = 1;
-  dim3 grid((M + BM - 1) / BM, (maxN + BN - 1) / BN, n_seg);
-  if (r_pad == 0) return launch_gemm<128, 0, 3, false>(p, grid, st);
-  if (r_pad == 16) return launch_gemm<128, 16, 3, false>(p, grid, st);
-  return launch_gemm<128, 32, 2, false>(p, grid, st);
+  p.n_seg = n_seg;
+  p.m_tiles = (M + BM - 1) / BM;
+  p.total_tiles = 0;
+  for (int i = 0; i < n_seg; ++i) p.total_tiles += p.seg[i].n_tiles * p.m_tiles;
+  dim3 grid(p.total_tiles);
+  if (BN == 256) return launch_gemm<256, 0, 3, false>(p, grid, st);
+  if (r_pad == 0) return launch_gemm<128, 0, 6, false>(p, grid, st);
+  if (r_pad == 16) return launch_gemm<128, 16, 5, false>(p, grid, st);
+  return launch_gemm<128, 32, 4, false>(p, grid, st);
 }
 
 int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const topo_linear_t* seg, cudaStream_t st) {
   TOPO_CHECK(C % BK == 0, TOPO_E_INVAL, "conv3x3: C (%d) must be a multiple of 64", C);
   TOPO_CHECK(x_ld % 8 == 0, TOPO_E_INVAL, "conv3x3: x_ld must be a multiple of 8");
   TOPO_CHECK(seg->r_pad == 0, TOPO_E_INVAL, "conv3x3: LoRA not supported on convolutions");
-  constexpr int BN = 128;
+  TOPO_CHECK(seg->act != TOPO_ACT_GEGLU, TOPO_E_INVAL, "conv3x3: GEGLU epilogue not supported on convolutions");
+  const int BN = pick_bn((B * H * W + BM - 1) / BM, seg->N, 0, 1, seg->act);
   GemmParams p;
   memset(&p, 0, sizeof(p));
   const int bw = W < BM ? W : BM;
@@ -461,8 +630,12 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   p.tiles_w = W / bw;
   p.tiles_h = H / bh;
   const int tiles_b = (B + bb - 1) / bb;
-  dim3 grid(p.tiles_w * p.tiles_h * tiles_b, (seg->N + BN - 1) / BN, 1);
-  return launch_gemm<128, 0, 3, true>(p, grid, st);
+  p.n_seg = 1;
+  p.m_tiles = p.tiles_w * p.tiles_h * tiles_b;
+  p.total_tiles = p.seg[0].n_tiles * p.m_tiles;
+  dim3 grid(p.total_tiles);
+  if (BN == 256) return launch_gemm<256, 0, 3, true>(p, grid, st);
+  return launch_gemm<128, 0, 6, true>(p, grid, st);
 }
 
 }  // namespace topo

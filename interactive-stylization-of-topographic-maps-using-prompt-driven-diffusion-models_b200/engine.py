@@ -48,21 +48,21 @@ class _Prof:
 PROF = _Prof()
 
 
-def _rec(kind: str, flops: float, nbytes: float, fn):
+def _rec(kind: str, flops: float, nbytes: float, fn, tag: str = ""):
     if not PROF.on:
         return fn()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     r = fn()
     e1.record()
-    PROF.recs.append((kind, flops, nbytes, e0, e1))
+    PROF.recs.append((kind, flops, nbytes, e0, e1, tag))
     return r
 
 
 def prof_summary() -> Dict[str, Dict[str, float]]:
     """kind -> {launches, ms, flops, bytes}; call after torch.cuda.synchronize()."""
     out: Dict[str, Dict[str, float]] = {}
-    for kind, fl, nb, e0, e1 in PROF.recs:
+    for kind, fl, nb, e0, e1, _tag in PROF.recs:
         d = out.setdefault(kind, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
         d["launches"] += 1
         d["ms"] += e0.elapsed_time(e1)
@@ -131,13 +131,9 @@ def pack_conv3x3(conv: nn.Conv2d, device) -> Lin:
 
 
 def pack_geglu(mod: nn.Module, device) -> Lin:
-    """GEGLU ``proj`` with rows interleaved per 128-row tile (64 values | 64 gates) for the fused epilogue."""
+    """GEGLU ``proj`` with rows interleaved per kernel N tile (values | gates) for the fused epilogue."""
     lin = pack_linear(mod, device)
-    inner, half = lin.N // 2, 64
-    idx = []
-    for t in range(inner // half):
-        idx += list(range(t * half, (t + 1) * half)) + list(range(inner + t * half, inner + (t + 1) * half))
-    idx = torch.tensor(idx, device=device)
+    idx = ops.geglu_index(lin.N, device)
     lin.W = lin.W[idx].contiguous()
     lin.bias = None if lin.bias is None else lin.bias[idx].contiguous()
     lin.B = None if lin.B is None else lin.B[idx].contiguous()
@@ -174,7 +170,7 @@ def gemm(x: torch.Tensor, lin: Lin, out: Optional[torch.Tensor] = None, out_col:
                       rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=rows_per_group, act=act)
     fl = 2.0 * M * lin.N * lin.K + 2.0 * M * lin.r * (lin.K + lin.N)
     _rec("gemm_lora" if lin.r else "gemm", fl, 2.0 * (M * lin.K + lin.N * lin.K + M * n_out),
-         lambda: ops.lora_linear_raw(x, M, lin.K, x.stride(0), [seg]))
+         lambda: ops.lora_linear_raw(x, M, lin.K, x.stride(0), [seg]), f"M{M} N{lin.N} K{lin.K} act{act} res{int(res is not None)}")
     _count()
     return out
 
@@ -189,7 +185,7 @@ def gemm_multi(x: torch.Tensor, lins: Sequence[Lin], out: torch.Tensor, cols: Se
         fl = sum(2.0 * M * l.N * K + 2.0 * M * l.r * (K + l.N) for l in lins)
         nb = 2.0 * (M * K + sum(l.N * K + M * l.N for l in lins))
         _rec("gemm_lora" if any(l.r for l in lins) else "gemm", fl, nb,
-             lambda: ops.lora_linear_raw(x, M, K, x.stride(0), segs))
+             lambda: ops.lora_linear_raw(x, M, K, x.stride(0), segs), f"M{M} N{'+'.join(str(l.N) for l in lins)} K{K} multi")
         _count()
     else:
         for l, c in zip(lins, cols):
@@ -208,7 +204,7 @@ def conv3(x: torch.Tensor, B: int, H: int, W: int, lin: Lin, out: Optional[torch
                       rowbias_ld=0 if rowbias is None else rowbias.stride(0), rows_per_group=H * W)
     M = B * H * W
     _rec("conv3x3", 2.0 * M * lin.N * 9 * C, 2.0 * (M * C + lin.N * 9 * C + M * lin.N),
-         lambda: ops.conv3x3_raw(x, B, H, W, C, x.stride(0), seg))
+         lambda: ops.conv3x3_raw(x, B, H, W, C, x.stride(0), seg), f"B{B} H{H} C{C} N{lin.N} res{int(res is not None)}")
     _count()
     return out
 
@@ -369,7 +365,8 @@ def run_attn(a: PAttn, n: torch.Tensor, h: torch.Tensor, B: int, kv) -> torch.Te
         k, v = kv
     Nk = k.shape[1]
     o = _rec("attn_self" if kv is None else "attn_cross", 4.0 * B * a.heads * N * Nk * a.d,
-             2.0 * (2 * M * hdp + 2 * B * Nk * hdp), lambda: ops.attention(q, k, v, a.heads, a.dp, a.scale))
+             2.0 * (2 * M * hdp + 2 * B * Nk * hdp), lambda: ops.attention(q, k, v, a.heads, a.dp, a.scale),
+             f"B{B} N{N} Nk{Nk} d{a.d}")
     _count()
     out = gemm(o.view(M, hdp), a.o, res=h)
     if getattr(a.module, "control_states", None) is not None:  # CrossAttention_LoRA_Control (attention_lora.py:73-81)

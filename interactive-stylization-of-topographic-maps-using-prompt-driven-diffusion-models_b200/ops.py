@@ -73,9 +73,23 @@ def pad_head_cols(W: torch.Tensor, heads: int, d: int, dp: int) -> torch.Tensor:
     return out.reshape(W.shape[0], heads * dp).contiguous()
 
 
-def geglu_interleave(W: torch.Tensor, bias: Optional[torch.Tensor], tile: int = 128):
-    """Reorder the rows of GEGLU ``proj`` ([2*inner, K]: first half values, second half gates) so every
-    128-row tile holds 64 value rows followed by their 64 gate rows (the fused epilogue pairs them)."""
+def geglu_index(n_rows: int, device) -> torch.Tensor:
+    """Row permutation for GEGLU ``proj`` ([2*inner, K]: first half values, second half gates): every N tile of the
+    kernel (``topo_geglu_tile(N)`` = 128 or 256 rows) holds tile/2 value rows followed by their tile/2 gate rows."""
+    tile = capi.load_library().topo_geglu_tile(n_rows)
+    inner, half = n_rows // 2, tile // 2
+    assert inner % half == 0
+    idx = []
+    for t in range(inner // half):
+        idx += list(range(t * half, (t + 1) * half)) + list(range(inner + t * half, inner + (t + 1) * half))
+    return torch.tensor(idx, device=device)
+
+
+def geglu_interleave(W: torch.Tensor, bias: Optional[torch.Tensor], tile: Optional[int] = None):
+    """Apply ``geglu_index`` to the weight rows (and bias) of a GEGLU projection."""
+    if tile is None:
+        idx = geglu_index(W.shape[0], W.device)
+        return W[idx].contiguous(), (None if bias is None else bias[idx].contiguous())
     inner = W.shape[0] // 2
     half = tile // 2
     assert inner % half == 0
