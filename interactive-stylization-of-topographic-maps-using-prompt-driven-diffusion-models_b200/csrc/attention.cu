@@ -3,9 +3,10 @@
 // One CTA owns a 128-row query tile of one (batch, head) and streams 128-key blocks:
 //   S   = Q K_j^T        UMMA M=128 N=128 K=dp   (both operands K-major, SWIZZLE_128B, TMA fed)  -> TMEM [0,128)
 //   P   = exp2(S*c - m)  4 softmax warps, one accumulator row per thread (row == TMEM lane, so max / sum need
-//                        no shuffles); P is written bf16 into a swizzled smem tile (A operand of the next UMMA)
-//   Ob  = P V_j          UMMA M=128 N=dp K=128, V consumed MN-major straight from its [keys, dp] TMA tile
-//                        -> TMEM [128,128+dp); folded into fp32 registers  O = O*alpha + Ob  (online softmax)
+//                        no shuffles); S is read from TMEM once; P is written bf16 into a swizzled smem tile
+//   O  += P V_j          UMMA M=128 N=dp K=128, V consumed MN-major straight from its [keys, dp] TMA tile, accumulated
+//                        in TMEM [128,128+dp) across key blocks; rescaled in place (tcgen05.ld/st) only when the
+//                        running row max moves by more than 2^8 (lazy online softmax)
 // Self-attention (Nk = Nq in {64..4096}) and 77-token cross-attention (one masked block, both CFG branches
 // batched along B) are the same kernel.  K/V tiles rotate through a 3-slot smem ring.
 // warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = softmax / correction / epilogue.
@@ -39,7 +40,7 @@ struct AttnSmem {
 };
 
 template <int DP>
-__global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_constant__ AttnParams p) {
+__global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_kernel(const __grid_constant__ AttnParams p) {
   using L = AttnSmem<DP>;
   constexpr int ATOMS = L::ATOMS;
   extern __shared__ uint8_t smem_raw[];
@@ -52,9 +53,10 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
   uint64_t* kv_full = bars + 1;              // [RING]
   uint64_t* kv_empty = kv_full + ATT_RING;   // [RING]
   uint64_t* s_full = kv_empty + ATT_RING;
-  uint64_t* p_ready = s_full + 1;            // 128 arrivals: P_j in smem, S_j and Ob_{j-1} consumed
+  uint64_t* p_ready = s_full + 1;            // 128 arrivals: P_j in smem (and O rescaled if the row max moved)
   uint64_t* pv_done = s_full + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 3);
+  uint64_t* s_free = s_full + 3;             // 128 arrivals: S_j is in registers, the S accumulator may be overwritten
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -76,6 +78,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     mbar_init(s_full, 1);
     mbar_init(p_ready, 128);
     mbar_init(pv_done, 1);
+    mbar_init(s_free, 128);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, L::TMEM_COLS);
@@ -128,8 +131,12 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
       mbar_wait(q_full, 0);
       issue_s(0);
       for (int j = 0; j < nblk; ++j) {
-        mbar_wait(p_ready, j & 1);  // P_j written, S_j fully read, Ob_{j-1} folded
-        if (j + 1 < nblk) issue_s(j + 1);
+        if (j + 1 < nblk) {
+          mbar_wait(s_free, j & 1);  // S_j is in the softmax warps' registers
+          tc_fence_after();
+          issue_s(j + 1);            // overlaps softmax(j)
+        }
+        mbar_wait(p_ready, j & 1);   // P_j written; O rescaled when needed
         const int t = 2 * j + 1, slot = t % ATT_RING;
         mbar_wait(&kv_full[slot], (t / ATT_RING) & 1);
         tc_fence_after();
@@ -138,7 +145,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
         for (int k = 0; k < ATT_BN / 16; ++k) {
           const uint64_t pd = kmajor_desc(p_s + (k >> 2) * 16384 + (k & 3) * 32, 128);
           const uint64_t vd = mnmajor_sw128_desc(v_s + k * 2048, 16384);
-          umma_bf16(tmem_o, pd, vd, idesc_pv, k != 0);
+          umma_bf16(tmem_o, pd, vd, idesc_pv, (j | k) != 0);  // O accumulates in TMEM across key blocks
         }
         umma_commit(pv_done);
         umma_commit(&kv_empty[slot]);
@@ -146,73 +153,87 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     }
   } else {
     // ===================== softmax / correction / epilogue =====================
+    // One query row per thread (row == TMEM lane: max / sum need no shuffles).  S_j is read from TMEM ONCE into
+    // registers; O accumulates in TMEM across key blocks and is rescaled only when the running row max moves by more
+    // than 2^8 (lazy rescaling: P stays <= 256, exact after the final division by the running sum).
     const int qd = warp & 3;
     const int row = qd * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
-    float o_acc[DP];
-#pragma unroll
-    for (int i = 0; i < DP; ++i) o_acc[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f, alpha_pend = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
     const float c = p.scale_log2e;
-
-    auto fold_o = [&](float alpha) {
-      // o_acc = o_acc * alpha + Ob  (Ob: DP fp32 columns at tmem_o)
-#pragma unroll
-      for (int c0 = 0; c0 < DP; c0 += 32) {
-        float t[32];
-        if (DP - c0 >= 32) {
-          tmem_ld32(tmem_o + lane_addr + c0, t);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o_acc[c0 + i] = fmaf(o_acc[c0 + i], alpha, t[i]);
-        } else {
-          tmem_ld16(tmem_o + lane_addr + c0, t);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 16; ++i) o_acc[c0 + i] = fmaf(o_acc[c0 + i], alpha, t[i]);
-        }
-      }
-    };
+    constexpr float RESCALE_THRESHOLD = 8.0f;
 
     for (int j = 0; j < nblk; ++j) {
       const int kvalid = min(ATT_BN, p.Nk - j * ATT_BN);
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      // ---- pass 1: row max over the block
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
-        float v[32];
-        tmem_ld32(tmem_s + lane_addr + cc * 32, v);
-        tmem_ld_wait();
+      float sv[ATT_BN];
+      float mxp[8];
+      // two half loads: the max over the first 64 columns overlaps the TMEM read of the second 64; eight independent
+      // max chains (a single chain would be 127 dependent FMNMX = ~600 cycles per block)
+      tmem_ld32(tmem_s + lane_addr, sv);
+      tmem_ld32(tmem_s + lane_addr + 32, sv + 32);
+      tmem_ld_wait();
+      tmem_ld32(tmem_s + lane_addr + 64, sv + 64);
+      tmem_ld32(tmem_s + lane_addr + 96, sv + 96);
+      if (kvalid < ATT_BN) {  // last (or only: 77-token cross-attention) block: keys beyond Nk do not exist
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (cc * 32 + i < kvalid) mx = fmaxf(mx, v[i]);
+        for (int i = 0; i < 64; ++i)
+          if (i >= kvalid) sv[i] = -INFINITY;
       }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mxp[k] = sv[k];
+#pragma unroll
+      for (int i = 8; i < 64; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], sv[i]);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(s_free);
+      if (kvalid < ATT_BN) {
+#pragma unroll
+        for (int i = 64; i < ATT_BN; ++i)
+          if (i >= kvalid) sv[i] = -INFINITY;
+      }
+#pragma unroll
+      for (int i = 64; i < ATT_BN; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], sv[i]);
+      const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])), fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
       const float m_new = fmaxf(m_run, mx * c);
-      const float alpha = fast_exp2(m_run - m_new);
-      m_run = m_new;
-      l_run *= alpha;
-      // ---- fold the previous block's P V into the register accumulator
+      const bool need = j > 0 && m_new > m_run + RESCALE_THRESHOLD;
+      if (j == 0) m_run = m_new;
       if (j > 0) {
-        mbar_wait(pv_done, (j - 1) & 1);
+        mbar_wait(pv_done, (j - 1) & 1);  // P_{j-1} V_{j-1} finished: the P tile is free and O is up to date
         tc_fence_after();
-        fold_o(alpha_pend);
+        if (__any_sync(0xffffffffu, need)) {
+          const float alpha = need ? fast_exp2(m_run - m_new) : 1.0f;
+          if (need) {
+            m_run = m_new;
+            l_run *= alpha;
+          }
+#pragma unroll
+          for (int c0 = 0; c0 < DP; c0 += 16) {
+            float t[16];
+            tmem_ld16(tmem_o + lane_addr + c0, t);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) t[i] *= alpha;
+            tmem_st16(tmem_o + lane_addr + c0, t);
+          }
+          tmem_st_wait();
+        }
       }
-      alpha_pend = alpha;
-      // ---- pass 2: probabilities -> bf16 -> swizzled smem tile
-      float lsum = 0.f;
-#pragma unroll 1
+      // ---- probabilities -> bf16 -> swizzled smem tile (A operand of the P V UMMA)
+      float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;  // independent sum chains
+      const float nm = -m_run;
+#pragma unroll
       for (int cc = 0; cc < 4; ++cc) {
-        float v[32];
-        tmem_ld32(tmem_s + lane_addr + cc * 32, v);
-        tmem_ld_wait();
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          float e0 = (cc * 32 + i < kvalid) ? fast_exp2(fmaf(v[i], c, -m_new)) : 0.f;
-          float e1 = (cc * 32 + i + 1 < kvalid) ? fast_exp2(fmaf(v[i + 1], c, -m_new)) : 0.f;
-          lsum += e0 + e1;
+          const float e0 = fast_exp2(fmaf(sv[cc * 32 + i], c, nm));
+          const float e1 = fast_exp2(fmaf(sv[cc * 32 + i + 1], c, nm));
+          if ((i & 6) == 0) ls0 += e0 + e1;
+          else if ((i & 6) == 2) ls1 += e0 + e1;
+          else if ((i & 6) == 4) ls2 += e0 + e1;
+          else ls3 += e0 + e1;
           pk[i >> 1] = pack_bf16x2(e0, e1);
         }
         uint8_t* base = p_tile + (cc >> 1) * 16384 + row * 128;
@@ -222,7 +243,7 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
           *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[jj * 4], pk[jj * 4 + 1], pk[jj * 4 + 2], pk[jj * 4 + 3]);
         }
       }
-      l_run += lsum;
+      l_run += (ls0 + ls1) + (ls2 + ls3);
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(p_ready);
@@ -230,19 +251,22 @@ __global__ void __launch_bounds__(ATT_THREADS, 1) attention_kernel(const __grid_
     // ---- last block's P V, normalise, store
     mbar_wait(pv_done, (nblk - 1) & 1);
     tc_fence_after();
-    fold_o(alpha_pend);
     const int qrow = q0 + row;
-    if (qrow < p.Nq) {
-      const float inv = 1.0f / l_run;
-      bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
+    const float inv = 1.0f / l_run;
+    bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
 #pragma unroll
-      for (int i = 0; i < DP; i += 8) {
-        uint4 u;
-        u.x = pack_bf16x2(o_acc[i] * inv, o_acc[i + 1] * inv);
-        u.y = pack_bf16x2(o_acc[i + 2] * inv, o_acc[i + 3] * inv);
-        u.z = pack_bf16x2(o_acc[i + 4] * inv, o_acc[i + 5] * inv);
-        u.w = pack_bf16x2(o_acc[i + 6] * inv, o_acc[i + 7] * inv);
-        *reinterpret_cast<uint4*>(dst + i) = u;
+    for (int c0 = 0; c0 < DP; c0 += 16) {
+      float t[16];
+      tmem_ld16(tmem_o + lane_addr + c0, t);
+      tmem_ld_wait();
+      if (qrow < p.Nq) {
+        uint4 u0, u1;
+        u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
+        u0.z = pack_bf16x2(t[4] * inv, t[5] * inv);   u0.w = pack_bf16x2(t[6] * inv, t[7] * inv);
+        u1.x = pack_bf16x2(t[8] * inv, t[9] * inv);   u1.y = pack_bf16x2(t[10] * inv, t[11] * inv);
+        u1.z = pack_bf16x2(t[12] * inv, t[13] * inv); u1.w = pack_bf16x2(t[14] * inv, t[15] * inv);
+        *reinterpret_cast<uint4*>(dst + c0) = u0;
+        *reinterpret_cast<uint4*>(dst + c0 + 8) = u1;
       }
     }
     __syncwarp();
