@@ -12,6 +12,7 @@
 // warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = softmax / correction / epilogue.
 // dp = 48 keeps smem at ~97 KB and TMEM at 256 columns so two CTAs share an SM: one CTA's softmax (MUFU bound)
 // overlaps the other's UMMAs.
+#include <stdlib.h>
 #include "common.cuh"
 #include "topo_b200.h"
 
@@ -19,8 +20,7 @@ namespace topo {
 
 constexpr int ATT_BM = 128;   // query rows per CTA
 constexpr int ATT_BN = 128;   // keys per block
-constexpr int ATT_THREADS = 192;
-constexpr int ATT_RING = 3;
+constexpr int ATT_THREADS = 320;  // TMA warp, MMA warp, 8 softmax warps
 
 struct alignas(64) AttnParams {
   CUtensorMap tm_q, tm_k, tm_v;  // 3-D (cols, rows, batch), box (64, 128, 1), SW128
@@ -33,29 +33,36 @@ template <int DP>
 struct AttnSmem {
   static constexpr int ATOMS = (DP + 63) / 64;
   static constexpr int TILE_BYTES = ATOMS * ATT_BM * 128;  // one Q / K / V tile: ATOMS x [128 rows x 128 B]
-  static constexpr int P_BYTES = ATT_BM * ATT_BN * 2;      // 2 atoms x 16 KB
-  static constexpr int BAR_OFF = TILE_BYTES * (1 + ATT_RING) + P_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
-  static constexpr uint32_t TMEM_COLS = (128 + DP) <= 256 ? 256 : 512;
+  static constexpr int RING = 3;                           // K/V tiles in flight
+  static constexpr int BAR_OFF = TILE_BYTES * (1 + RING);
+  static constexpr int TOTAL = BAR_OFF + 128;              // dp = 48: 64 KB -> smem never limits the two CTAs per SM
+  // TMEM columns: S fp32 [0,128) | O fp32 [128,128+DP) | P bf16x2 [P_COL, P_COL+64)
+  static constexpr uint32_t P_COL = 128 + ((DP + 15) / 16) * 16;
+  static constexpr uint32_t TMEM_COLS = (P_COL + 64) <= 256 ? 256 : 512;
 };
 
-template <int DP>
-__global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_kernel(const __grid_constant__ AttnParams p) {
+// NPOLY of every 8 element pairs of a softmax row take the FMA-pipe exp2 (exp2_poly2) instead of MUFU.EX2: at dp = 48
+// a 128x128 block needs 16384 exponentials = 1024 MUFU cycles per SM but only 384 tensor cycles, so the kernel is
+// MUFU-bound; moving 3/8 of them to FFMA2/FADD2 balances the MUFU against the issue slots.
+template <int DP, int NPOLY>
+__global__ void __launch_bounds__(ATT_THREADS, (DP == 48) ? 2 : 1) attention_kernel(const __grid_constant__ AttnParams p) {
   using L = AttnSmem<DP>;
   constexpr int ATOMS = L::ATOMS;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int ATT_RING = L::RING;
+  // the kernel has no static shared memory, so the dynamic window starts at the CTA's (1 KB aligned) base; the
+  // SWIZZLE_128B tiles need that alignment and the check below turns a violation into a launch failure
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* q_tile = smem;
   uint8_t* ring = smem + L::TILE_BYTES;
-  uint8_t* p_tile = ring + ATT_RING * L::TILE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
   uint64_t* q_full = bars;
   uint64_t* kv_full = bars + 1;              // [RING]
   uint64_t* kv_empty = kv_full + ATT_RING;   // [RING]
   uint64_t* s_full = kv_empty + ATT_RING;
   uint64_t* p_ready = s_full + 1;            // 128 arrivals: P_j in smem (and O rescaled if the row max moved)
-  uint64_t* pv_done = s_full + 2;
-  uint64_t* s_free = s_full + 3;             // 128 arrivals: S_j is in registers, the S accumulator may be overwritten
+  uint64_t* pv_done = s_full + 2;            // P_j V_j finished: O is up to date and the P columns are free
+  uint64_t* s_free = s_full + 3;             // 256 arrivals: S_j is in registers, the S accumulator may be overwritten
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_full + 4);
 
   const int warp = threadIdx.x >> 5;
@@ -76,9 +83,9 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
       mbar_init(&kv_empty[i], 1);
     }
     mbar_init(s_full, 1);
-    mbar_init(p_ready, 128);
+    mbar_init(p_ready, 256);
     mbar_init(pv_done, 1);
-    mbar_init(s_free, 128);
+    mbar_init(s_free, 256);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, L::TMEM_COLS);
@@ -88,6 +95,7 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_s = tmem_base;
   const uint32_t tmem_o = tmem_base + 128;
+  const uint32_t tmem_p = tmem_base + L::P_COL;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -114,7 +122,6 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, DP, 0, 1);  // B (= V) is MN-major
       const uint32_t q_s = smem_u32(q_tile);
-      const uint32_t p_s = smem_u32(p_tile);
       auto issue_s = [&](int j) {
         const int t = 2 * j, slot = t % ATT_RING;
         mbar_wait(&kv_full[slot], (t / ATT_RING) & 1);
@@ -143,9 +150,9 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
         const uint32_t v_s = smem_u32(ring + slot * L::TILE_BYTES);
 #pragma unroll
         for (int k = 0; k < ATT_BN / 16; ++k) {
-          const uint64_t pd = kmajor_desc(p_s + (k >> 2) * 16384 + (k & 3) * 32, 128);
           const uint64_t vd = mnmajor_sw128_desc(v_s + k * 2048, 16384);
-          umma_bf16(tmem_o, pd, vd, idesc_pv, (j | k) != 0);  // O accumulates in TMEM across key blocks
+          // A = P_j straight from TMEM (16 keys = 8 packed columns per step); O accumulates across key blocks
+          umma_bf16_ts(tmem_o, tmem_p + k * 8, vd, idesc_pv, (j | k) != 0);
         }
         umma_commit(pv_done);
         umma_commit(&kv_empty[slot]);
@@ -153,56 +160,64 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
     }
   } else {
     // ===================== softmax / correction / epilogue =====================
-    // One query row per thread (row == TMEM lane: max / sum need no shuffles).  S_j is read from TMEM ONCE into
-    // registers; O accumulates in TMEM across key blocks and is rescaled only when the running row max moves by more
+    // TWO threads per query row: warps 2..5 take key columns [0,64) of the block, warps 6..9 columns [64,128)
+    // (row == TMEM lane, a warp reaches the lane quadrant warp % 4).  Eight softmax warps per CTA, two CTAs per SM
+    // -> four per scheduler: one warp's MUFU bursts and dependency stalls hide behind the others' FMA work (with one
+    // thread per row the kernel sat at 63 % XU / 40 % issue utilisation: latency bound, profiles/r01c_attention.md).
+    // The two halves of a row exchange their block maxima through smem + a 64-thread named barrier; S_j is read from
+    // TMEM once; O accumulates in TMEM across key blocks and is rescaled only when the running row max moves by more
     // than 2^8 (lazy rescaling: P stays <= 256, exact after the final division by the running sum).
     const int qd = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = qd * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
-    float m_run = -INFINITY, l_run = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;  // l_run: this thread's half of the row sum
     const float c = p.scale_log2e;
     constexpr float RESCALE_THRESHOLD = 8.0f;
+    constexpr int HB = ATT_BN / 2;  // columns per thread
+    // Exchange slots: the last 32 B (logical 16-byte chunks 6 and 7) of every row of the last Q atom are never read
+    // by the UMMAs (dp = 48 / 80 / 160 end 32 B or more before the atom does), so once Q has landed (s_full(0)) each row
+    // owns 8 private floats there: [buf][half] block maxima in chunk 6, the two partial row sums in chunk 7.
+    float* xmax = reinterpret_cast<float*>(q_tile + (ATOMS - 1) * 16384 + row * 128 + ((6 ^ (row & 7)) << 4));
+    float* xsum = reinterpret_cast<float*>(q_tile + (ATOMS - 1) * 16384 + row * 128 + ((7 ^ (row & 7)) << 4));
 
     for (int j = 0; j < nblk; ++j) {
-      const int kvalid = min(ATT_BN, p.Nk - j * ATT_BN);
+      const int kvalid = min(HB, max(0, p.Nk - j * ATT_BN - half * HB));  // valid keys among this thread's columns
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      float sv[ATT_BN];
-      float mxp[8];
-      // two half loads: the max over the first 64 columns overlaps the TMEM read of the second 64; eight independent
-      // max chains (a single chain would be 127 dependent FMNMX = ~600 cycles per block)
-      tmem_ld32(tmem_s + lane_addr, sv);
-      tmem_ld32(tmem_s + lane_addr + 32, sv + 32);
-      tmem_ld_wait();
-      tmem_ld32(tmem_s + lane_addr + 64, sv + 64);
-      tmem_ld32(tmem_s + lane_addr + 96, sv + 96);
-      if (kvalid < ATT_BN) {  // last (or only: 77-token cross-attention) block: keys beyond Nk do not exist
-#pragma unroll
-        for (int i = 0; i < 64; ++i)
-          if (i >= kvalid) sv[i] = -INFINITY;
-      }
-#pragma unroll
-      for (int k = 0; k < 8; ++k) mxp[k] = sv[k];
-#pragma unroll
-      for (int i = 8; i < 64; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], sv[i]);
+      float sv[HB];
+      tmem_ld32(tmem_s + lane_addr + half * HB, sv);
+      tmem_ld32(tmem_s + lane_addr + half * HB + 32, sv + 32);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(s_free);
-      if (kvalid < ATT_BN) {
+      if (kvalid < HB) {  // last (or only: 77-token cross-attention) block: keys beyond Nk do not exist
 #pragma unroll
-        for (int i = 64; i < ATT_BN; ++i)
+        for (int i = 0; i < HB; ++i)
           if (i >= kvalid) sv[i] = -INFINITY;
       }
+      float mxp[8];  // eight independent max chains
 #pragma unroll
-      for (int i = 64; i < ATT_BN; ++i) mxp[i & 7] = fmaxf(mxp[i & 7], sv[i]);
-      const float mx = fmaxf(fmaxf(fmaxf(mxp[0], mxp[1]), fmaxf(mxp[2], mxp[3])), fmaxf(fmaxf(mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7])));
+      for (int k = 0; k < 8; ++k) mxp[k] = sv[k];
+#pragma unroll
+      for (int i = 8; i < 56; i += 16)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) mxp[k] = fmax3(mxp[k], sv[i + k], sv[i + 8 + k]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mxp[k] = fmaxf(mxp[k], sv[56 + k]);
+      float mx = fmaxf(fmax3(mxp[0], mxp[1], mxp[2]), fmax3(mxp[3], mxp[4], mxp[5]));
+      mx = fmax3(mx, mxp[6], mxp[7]);
+      // exchange with the thread that owns the other half of this row (same quadrant, other warp)
+      xmax[(j & 1) * 2 + half] = mx;
+      named_bar_sync(1 + qd, 64);
+      mx = fmaxf(mx, xmax[(j & 1) * 2 + (half ^ 1)]);
       const float m_new = fmaxf(m_run, mx * c);
       const bool need = j > 0 && m_new > m_run + RESCALE_THRESHOLD;
       if (j == 0) m_run = m_new;
       if (j > 0) {
-        mbar_wait(pv_done, (j - 1) & 1);  // P_{j-1} V_{j-1} finished: the P tile is free and O is up to date
+        mbar_wait(pv_done, (j - 1) & 1);  // P_{j-1} V_{j-1} finished: the P columns are free and O is up to date
         tc_fence_after();
-        if (__any_sync(0xffffffffu, need)) {
+        if (__any_sync(0xffffffffu, need)) {  // both halves of a row take the same decision (same m_new, m_run)
           const float alpha = need ? fast_exp2(m_run - m_new) : 1.0f;
           if (need) {
             m_run = m_new;
@@ -210,6 +225,7 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
           }
 #pragma unroll
           for (int c0 = 0; c0 < DP; c0 += 16) {
+            if (((c0 >> 4) & 1) != half) continue;  // the halves split O's 16-column chunks
             float t[16];
             tmem_ld16(tmem_o + lane_addr + c0, t);
             tmem_ld_wait();
@@ -220,42 +236,44 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
           tmem_st_wait();
         }
       }
-      // ---- probabilities -> bf16 -> swizzled smem tile (A operand of the P V UMMA)
-      float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;  // independent sum chains
-      const float nm = -m_run;
+      // ---- probabilities -> packed bf16 pairs -> TMEM (A operand of the P V UMMA: row = lane, keys 2c, 2c+1 = column c)
+      float2 ls[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+      const float2 c2 = make_float2(c, c), nm2 = make_float2(-m_run, -m_run);
+      uint32_t pk[HB / 2];
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) {
-        uint32_t pk[16];
+      for (int cc = 0; cc < 2; ++cc) {
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float e0 = fast_exp2(fmaf(sv[cc * 32 + i], c, nm));
-          const float e1 = fast_exp2(fmaf(sv[cc * 32 + i + 1], c, nm));
-          if ((i & 6) == 0) ls0 += e0 + e1;
-          else if ((i & 6) == 2) ls1 += e0 + e1;
-          else if ((i & 6) == 4) ls2 += e0 + e1;
-          else ls3 += e0 + e1;
-          pk[i >> 1] = pack_bf16x2(e0, e1);
-        }
-        uint8_t* base = p_tile + (cc >> 1) * 16384 + row * 128;
-#pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-          const int chunk = ((cc & 1) * 4 + jj) ^ (row & 7);
-          *reinterpret_cast<uint4*>(base + chunk * 16) = make_uint4(pk[jj * 4], pk[jj * 4 + 1], pk[jj * 4 + 2], pk[jj * 4 + 3]);
+          const float2 x = ffma2(make_float2(sv[cc * 32 + i], sv[cc * 32 + i + 1]), c2, nm2);
+          float2 e;
+          if (((i >> 1) & 7) < NPOLY) {
+            e = exp2_poly2(x);
+          } else {
+            e.x = fast_exp2(x.x);
+            e.y = fast_exp2(x.y);
+          }
+          ls[(i >> 1) & 3] = fadd2(ls[(i >> 1) & 3], e);  // four independent packed sum chains
+          pk[cc * 16 + (i >> 1)] = pack_bf16x2(e.x, e.y);
         }
       }
-      l_run += (ls0 + ls1) + (ls2 + ls3);
-      fence_proxy_async_smem();
+      tmem_st32(tmem_p + lane_addr + half * (HB / 2), pk);
+      const float2 lsum = fadd2(fadd2(ls[0], ls[1]), fadd2(ls[2], ls[3]));
+      l_run += lsum.x + lsum.y;
+      tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_ready);
     }
-    // ---- last block's P V, normalise, store
+    // ---- row sum of both halves, last block's P V, normalise, store (the halves split O's 16-column chunks)
+    xsum[half] = l_run;
+    named_bar_sync(1 + qd, 64);
+    const float inv = 1.0f / (l_run + xsum[half ^ 1]);
     mbar_wait(pv_done, (nblk - 1) & 1);
     tc_fence_after();
     const int qrow = q0 + row;
-    const float inv = 1.0f / l_run;
     bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
 #pragma unroll
     for (int c0 = 0; c0 < DP; c0 += 16) {
+      if (((c0 >> 4) & 1) != half) continue;
       float t[16];
       tmem_ld16(tmem_o + lane_addr + c0, t);
       tmem_ld_wait();
@@ -280,10 +298,10 @@ __global__ void __launch_bounds__(ATT_THREADS, (DP <= 80) ? 2 : 1) attention_ker
   }
 }
 
-template <int DP>
+template <int DP, int NPOLY>
 static int launch_attention(const AttnParams& p, dim3 grid, cudaStream_t st) {
   using L = AttnSmem<DP>;
-  auto kfn = attention_kernel<DP>;
+  auto kfn = attention_kernel<DP, NPOLY>;
   static bool attr_set = false;
   if (!attr_set) {
     TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -292,6 +310,19 @@ static int launch_attention(const AttnParams& p, dim3 grid, cudaStream_t st) {
   kfn<<<grid, ATT_THREADS, L::TOTAL, st>>>(p);
   TOPO_CUDA(cudaGetLastError());
   return 0;
+}
+
+// Share of exponentials on the FMA pipes, in eighths.  Defaults are the measured optimum per head dim; the
+// TOPO_ATTN_NPOLY environment variable (read once) overrides it for tuning sweeps (tools/attn_sweep.py).
+static int attn_npoly(int dp) {
+  static int env = -2;
+  if (env == -2) {
+    const char* e = getenv("TOPO_ATTN_NPOLY");
+    env = e ? atoi(e) : -1;
+  }
+  if (env >= 0) return env;
+  (void)dp;
+  return 0;  // measured on B200 (profiles/r01c_attention.md): the kernel is issue/latency bound, not MUFU bound
 }
 
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
@@ -325,9 +356,17 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   p.ldo = ldo;
   p.scale_log2e = scale * 1.4426950408889634f;
   dim3 grid((Nq + ATT_BM - 1) / ATT_BM, heads, B);
-  if (dp == 48) return launch_attention<48>(p, grid, st);
-  if (dp == 80) return launch_attention<80>(p, grid, st);
-  return launch_attention<160>(p, grid, st);
+  const int np = attn_npoly(dp);
+  if (dp == 48) {
+    switch (np) {
+      case 1: return launch_attention<48, 1>(p, grid, st);
+      case 2: return launch_attention<48, 2>(p, grid, st);
+      case 3: return launch_attention<48, 3>(p, grid, st);
+      default: return launch_attention<48, 0>(p, grid, st);
+    }
+  }
+  if (dp == 80) return np >= 1 ? launch_attention<80, 2>(p, grid, st) : launch_attention<80, 0>(p, grid, st);
+  return launch_attention<160, 0>(p, grid, st);
 }
 
 }  // namespace topo

@@ -96,6 +96,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// named barrier among `nthreads` threads (whole warps) of the CTA; id 0 is __syncthreads
+// (immediate ids so that ptxas reserves 5 hardware barriers, not all 16)
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  switch (id) {
+    case 1: asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); break;
+    case 2: asm volatile("bar.sync 2, %0;" ::"r"(nthreads) : "memory"); break;
+    case 3: asm volatile("bar.sync 3, %0;" ::"r"(nthreads) : "memory"); break;
+    default: asm volatile("bar.sync 4, %0;" ::"r"(nthreads) : "memory"); break;
+  }
+}
+
 // ---- proxies / fences ---------------------------------------------------------------------------
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -187,6 +198,19 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with the A operand read from TMEM (M = 128: row = lane, two consecutive 16-bit K elements per 32-bit column,
+// i.e. 8 columns per K = 16 step); B from shared memory.
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 // Make `bar` complete when all previously issued tcgen05.mma of this thread have finished
 // (implies tcgen05.fence::before_thread_sync).
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -229,6 +253,17 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
       "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // ---- small math / packing ---------------------------------------------------------------------------
@@ -242,6 +277,55 @@ __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+// ---- packed fp32x2 arithmetic (FFMA2 / FADD2: one issue slot for two lanes of work) and the FMA-pipe exp2 ------------
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t d;
+  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)), "l"(*reinterpret_cast<uint64_t*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  uint64_t d;
+  asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fsub2(float2 a, float2 b) {
+  uint64_t d;
+  asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float2 fadd2_rm(float2 a, float2 b) {  // round towards -inf
+  uint64_t d;
+  asm("add.rm.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)));
+  return *reinterpret_cast<float2*>(&d);
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+// 2^x for a pair, x <= ~100, WITHOUT the MUFU: x = floor(x) + f; 2^f by a degree-3 minimax polynomial on [0,1)
+// (max rel. error 8.8e-5, far below the bf16 rounding of the probabilities it feeds); floor(x) enters through the
+// exponent field (the 1.5*2^23 trick: the low mantissa bits of x + magic ARE the integer, shifted in by one LEA).
+// per PAIR: 2 FMNMX + 3 FADD2 + 3 FFMA2 + 2 LEA; used on a fixed fraction of each softmax row so the
+// 16/clk/SM MUFU and the 128/clk/SM FMA pipes run side by side.
+__device__ __forceinline__ float2 exp2_poly2(float2 x) {
+  const float magic = 12582912.0f;  // 1.5 * 2^23
+  x.x = fmaxf(x.x, -126.0f);
+  x.y = fmaxf(x.y, -126.0f);
+  const float2 xr = fadd2_rm(x, make_float2(magic, magic));
+  const float2 fl = fadd2(xr, make_float2(-magic, -magic));
+  const float2 fr = fsub2(x, fl);  // fractional part in [0, 1)
+  float2 p = ffma2(fr, make_float2(0.077119089663028717f, 0.077119089663028717f),
+                   make_float2(0.227564394474029541f, 0.227564394474029541f));
+  p = ffma2(p, fr, make_float2(0.695146143436431885f, 0.695146143436431885f));
+  p = ffma2(p, fr, make_float2(1.0f, 1.0f));
+  float2 r;
+  r.x = __int_as_float(__float_as_int(p.x) + (__float_as_int(xr.x) << 23));
+  r.y = __int_as_float(__float_as_int(p.y) + (__float_as_int(xr.y) << 23));
+  return r;
 }
 __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
 // exact-erf GELU (upstream GEGLU uses F.gelu's erf form).  erf by Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7, far below
