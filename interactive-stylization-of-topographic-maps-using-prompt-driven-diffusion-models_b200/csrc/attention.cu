@@ -4,14 +4,14 @@
 // of a block lives in TMEM:
 //   S   = Q K_j^T        UMMA M=128 N=64 K=dp   (both operands K-major, SWIZZLE_128B, TMA fed)   -> TMEM S [0,64)
 //   P   = exp2(S*c - m)  4 softmax warps, one accumulator row per thread (row == TMEM lane, so max / sum need no
-//                        shuffles); P is packed to bf16 pairs and written back OVER S (columns [0,32))
+//                        shuffles); P is packed to bf16 pairs and written to its own TMEM columns [64,96)
 //   O  += P V_j          UMMA M=128 N=dp K=64 with A = P read straight from TMEM, V consumed MN-major from its
 //                        [keys, dp] TMA tile; O accumulates in TMEM across key blocks and is rescaled in place only
 //                        when the running row max moves by more than 2^8 (lazy online softmax)
-// Such a (128-row) chain is ONE strictly serial stream (S_j -> softmax_j -> P_j V_j -> S_j+1 ...), small enough that FOUR of
-// them share an SM at dp = 48 (112 TMEM columns -> 128 allocated, 40 KB smem, <= 80 registers): while one stream waits
-// on its UMMA round trip the other three keep the MUFU busy.  The earlier one-/two-CTA designs (128-key blocks, P in
-// shared memory) left every unit at ~65 % (profiles/r01c_attention.md): latency-, not throughput-bound.
+// S_{j+1} is issued as soon as S_j sits in the softmax warps' registers, so a stream (one 128-row query tile) never
+// waits on the tensor pipe; a stream needs 144 TMEM columns at dp = 48, and THREE of them (12 softmax warps) share a
+// CTA, one CTA per SM: the kernel is MUFU/issue bound and needs >= 3 warps per scheduler inside the exponentials to
+// keep the XU busy (profiles/r01c_attention.md has the measurements of the designs that led here).
 // Self-attention (Nk = Nq in {64..4096}) and 77-token cross-attention (masked last block, both CFG branches batched
 // along B) are the same kernel.  warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2..5 = softmax / correction /
 // epilogue.
@@ -36,7 +36,11 @@ struct alignas(64) AttnParams {
   float scale_log2e;
 };
 
-template <int DP, int NS>
+// EARLY = true: the layout above (P in its own columns, S_{j+1} issued under softmax(j)).
+// EARLY = false: P_j is written over S_j (columns [0,32)) and the issuer runs P_j V_j, then S_{j+1}: a stream then needs
+// only 64 + dp columns, so FOUR one-stream CTAs share an SM at dp = 48 — the better shape for the 77-key cross-attention
+// (two blocks per tile: prologue/epilogue bound, the UMMA round trip of one CTA hides behind the other three).
+template <int DP, int NS, bool EARLY>
 struct AttnSmem {
   static constexpr int THREADS = 32 * (1 + NS + 4 * NS);
   static constexpr int ATOMS = (DP + 63) / 64;
@@ -45,20 +49,22 @@ struct AttnSmem {
   static constexpr int RING = (DP == 160) ? 2 : 4;        // K/V tiles in flight (slot 0 = K, 1 = V when 2)
   static constexpr int BAR_OFF = NS * Q_BYTES + RING * KV_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256;
-  // TMEM columns per stream: S fp32 [0,64) (P bf16x2 aliases [0,32)) | O fp32 [64, 64+DP)
-  static constexpr uint32_t O_COL = ATT_BN;
-  static constexpr uint32_t STREAM_COLS = ATT_BN + ((DP + 15) / 16) * 16;
+  // TMEM columns per stream: S fp32 [0,64) | P bf16x2 [64,96) | O fp32 [96, 96+DP)
+  static constexpr uint32_t P_COL = EARLY ? ATT_BN : 0;
+  static constexpr uint32_t O_COL = EARLY ? ATT_BN + ATT_BN / 2 : ATT_BN;
+  static constexpr uint32_t STREAM_COLS = O_COL + ((DP + 15) / 16) * 16;
   static constexpr uint32_t TMEM_COLS = NS * STREAM_COLS <= 128 ? 128 : (NS * STREAM_COLS <= 256 ? 256 : 512);
-  static constexpr int CTAS = 512 / TMEM_COLS;            // resident CTAs per SM the kernel is sized for
+  static constexpr int CTAS_ALIAS = (512 / TMEM_COLS) > 3 ? 3 : (512 / TMEM_COLS);  // 4 would cap registers at 80 (spills)
+  static constexpr int CTAS = EARLY ? 512 / TMEM_COLS : CTAS_ALIAS;  // resident CTAs per SM the kernel is sized for
   static_assert(NS * STREAM_COLS <= 512, "TMEM");
   static_assert(CTAS * (TOTAL + 1024) <= 228 * 1024, "smem");
 };
 
 // NPOLY of every 8 element pairs of a softmax row take the FMA-pipe exp2 (exp2_poly2) instead of MUFU.EX2.
-template <int DP, int NS, int NPOLY>
-__global__ void __launch_bounds__(AttnSmem<DP, NS>::THREADS, AttnSmem<DP, NS>::CTAS)
+template <int DP, int NS, int NPOLY, bool EARLY>
+__global__ void __launch_bounds__(AttnSmem<DP, NS, EARLY>::THREADS, AttnSmem<DP, NS, EARLY>::CTAS)
 attention_kernel(const __grid_constant__ AttnParams p) {
-  using L = AttnSmem<DP, NS>;
+  using L = AttnSmem<DP, NS, EARLY>;
   constexpr int ATOMS = L::ATOMS;
   constexpr int RING = L::RING;
   // the kernel has no static shared memory, so the dynamic window starts at the CTA's (1 KB aligned) base; the
@@ -71,10 +77,11 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   uint64_t* q_full = bars;
   uint64_t* kv_full = bars + 1;          // [RING]
   uint64_t* kv_empty = kv_full + RING;   // [RING], one arrival per active stream
-  uint64_t* s_full = kv_empty + RING;    // [NS] S_j complete (implies P_{j-1} V_{j-1} complete: the tensor pipe is in order)
-  uint64_t* p_ready = s_full + NS;       // [NS] 128 arrivals: P_j is in TMEM (and O rescaled if the row max moved)
-  uint64_t* o_full = p_ready + NS;       // [NS] the last P V finished
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + NS);
+  uint64_t* s_full = kv_empty + RING;    // [NS] S_j complete
+  uint64_t* s_free = s_full + NS;        // [NS] 128 arrivals: S_j is in registers, S_{j+1} may overwrite it
+  uint64_t* p_ready = s_free + NS;       // [NS] 128 arrivals: P_j is in TMEM (and O rescaled if the row max moved)
+  uint64_t* pv_done = p_ready + NS;      // [NS] P_j V_j finished: O is up to date and the P columns are free
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + NS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -96,8 +103,9 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     }
     for (int i = 0; i < NS; ++i) {
       mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 128);
       mbar_init(&p_ready[i], 128);
-      mbar_init(&o_full[i], 1);
+      mbar_init(&pv_done[i], 1);
     }
     fence_barrier_init();
   }
@@ -133,6 +141,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     const int st = warp - 1;
     if (lane == 0 && st < nact) {
       const uint32_t tmem_s = tmem_base + st * L::STREAM_COLS;
+      const uint32_t tmem_p = tmem_s + L::P_COL;
       const uint32_t tmem_o = tmem_s + L::O_COL;
       uint64_t* s_full_b = &s_full[st];
       uint64_t* p_ready_b = &p_ready[st];
@@ -156,7 +165,12 @@ attention_kernel(const __grid_constant__ AttnParams p) {
       mbar_wait(q_full, 0);
       issue_s(0);
       for (int j = 0; j < nblk; ++j) {
-        mbar_wait(p_ready_b, j & 1);  // P_j written over S_j; O rescaled when needed
+        if (EARLY && j + 1 < nblk) {
+          mbar_wait(&s_free[st], j & 1);  // S_j is in the softmax warps' registers
+          tc_fence_after();
+          issue_s(j + 1);                 // runs under softmax(j)
+        }
+        mbar_wait(p_ready_b, j & 1);      // P_j written; O rescaled when needed
         const int t = 2 * j + 1, slot = t % RING;
         mbar_wait(&kv_full[slot], (t / RING) & 1);
         tc_fence_after();
@@ -165,84 +179,65 @@ attention_kernel(const __grid_constant__ AttnParams p) {
         for (int k = 0; k < ATT_BN / 16; ++k) {
           const uint64_t vd = mnmajor_sw128_desc(v_s + k * 2048, L::KV_ATOM);
           // A = P_j straight from TMEM (16 keys = 8 packed columns per step); O accumulates across key blocks
-          umma_bf16_ts(tmem_o, tmem_s + k * 8, vd, idesc_pv, (j | k) != 0);
+          umma_bf16_ts(tmem_o, tmem_p + k * 8, vd, idesc_pv, (j | k) != 0);
         }
+        umma_commit(&pv_done[st]);
         umma_commit(&kv_empty[slot]);
-        if (j + 1 < nblk) issue_s(j + 1);  // overwrites P_j only after P_j V_j (the tensor pipe runs in issue order)
-        else umma_commit(&o_full[st]);
+        if (!EARLY && j + 1 < nblk) issue_s(j + 1);  // overwrites P_j after P_j V_j (the tensor pipe runs in issue order)
       }
     }
   } else {
     // ===================== softmax / correction / epilogue =====================
-    // One query row per thread (row == TMEM lane: max / sum need no shuffles).  Registers are the budget that lets four
-    // CTAs share an SM, so S_j is walked in 32-column halves A = [0,32), B = [32,64): max(A), max(B) (B stays in
-    // registers), exp(B) -> 16 packed words, re-read A from TMEM (cheap), store P_B over S columns [16,32) (A is in
-    // registers by then), exp(A), store P_A over columns [0,16).
+    // One query row per thread (row == TMEM lane: max / sum need no shuffles).  S_j is read from TMEM once (s_free then
+    // lets the issuer start S_{j+1} under this softmax), P_j goes to its own TMEM columns as packed bf16 pairs, O is
+    // rescaled in place only when the running row max moved by more than 2^8 (P stays <= 256; exact after the final
+    // division by the running sum).
     const int qd = warp & 3;  // the TMEM lane quadrant a warp can reach is warp % 4
     const int st = (warp - 1 - NS) >> 2;
     const int row = qd * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
     const uint32_t tmem_s = tmem_base + st * L::STREAM_COLS;
+    const uint32_t tmem_p = tmem_s + L::P_COL;
     const uint32_t tmem_o = tmem_s + L::O_COL;
     uint64_t* s_full_b = &s_full[st];
     uint64_t* p_ready_b = &p_ready[st];
+    uint64_t* pv_done_b = &pv_done[st];
     const int nblk_st = st < nact ? nblk : 0;  // a stream without query rows idles
     float m_run = -INFINITY, l_run = 0.f;
     const float c = p.scale_log2e;
     constexpr float RESCALE_THRESHOLD = 8.0f;
 
-    auto mask32 = [](float* v, int nvalid) {  // keys beyond Nk do not exist (last block; 77-token cross-attention)
-      if (nvalid < 32) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (i >= nvalid) v[i] = -INFINITY;
-      }
-    };
-    auto max32 = [](const float* v) {
-      float m0 = fmax3(v[0], v[1], v[2]), m1 = fmax3(v[3], v[4], v[5]), m2 = fmax3(v[6], v[7], v[8]), m3 = fmax3(v[9], v[10], v[11]);
-      m0 = fmax3(m0, v[12], v[13]); m1 = fmax3(m1, v[14], v[15]); m2 = fmax3(m2, v[16], v[17]); m3 = fmax3(m3, v[18], v[19]);
-      m0 = fmax3(m0, v[20], v[21]); m1 = fmax3(m1, v[22], v[23]); m2 = fmax3(m2, v[24], v[25]); m3 = fmax3(m3, v[26], v[27]);
-      m0 = fmax3(m0, v[28], v[29]); m1 = fmax3(m1, v[30], v[31]);
-      return fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-    };
-    // 32 scores -> 16 packed bf16 pairs of exp2(s*c - m); returns the (fp32) sum of the 32 probabilities
-    auto exp32 = [&](const float* v, uint32_t* pk, float2 c2, float2 nm2) {
-      float2 ls0 = make_float2(0.f, 0.f), ls1 = ls0;
-#pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        const float2 x = ffma2(make_float2(v[i], v[i + 1]), c2, nm2);
-        float2 e;
-        if (((i >> 1) & 7) < NPOLY) {
-          e = exp2_poly2(x);
-        } else {
-          e.x = fast_exp2(x.x);
-          e.y = fast_exp2(x.y);
-        }
-        if (i & 2) ls1 = fadd2(ls1, e);
-        else ls0 = fadd2(ls0, e);
-        pk[i >> 1] = pack_bf16x2(e.x, e.y);
-      }
-      ls0 = fadd2(ls0, ls1);
-      return ls0.x + ls0.y;
-    };
-
     for (int j = 0; j < nblk_st; ++j) {
       const int kvalid = min(ATT_BN, p.Nk - j * ATT_BN);
-      mbar_wait(s_full_b, j & 1);  // S_j complete, and with it P_{j-1} V_{j-1}: O is up to date
+      mbar_wait(s_full_b, j & 1);
       tc_fence_after();
-      float va[32], vb[32];
-      tmem_ld32(tmem_s + lane_addr, va);
+      float sv[ATT_BN];
+      tmem_ld32(tmem_s + lane_addr, sv);
+      tmem_ld32(tmem_s + lane_addr + 32, sv + 32);
       tmem_ld_wait();
-      mask32(va, kvalid);
-      float mx = max32(va);
-      tmem_ld32(tmem_s + lane_addr + 32, vb);
-      tmem_ld_wait();
-      mask32(vb, kvalid - 32);
-      mx = fmaxf(mx, max32(vb));
+      tc_fence_before();
+      mbar_arrive(&s_free[st]);
+      if (kvalid < ATT_BN) {  // last (or only: 77-token cross-attention) block: keys beyond Nk do not exist
+#pragma unroll
+        for (int i = 0; i < ATT_BN; ++i)
+          if (i >= kvalid) sv[i] = -INFINITY;
+      }
+      float mxp[8];  // eight independent max chains
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mxp[k] = sv[k];
+#pragma unroll
+      for (int i = 8; i < 56; i += 16)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) mxp[k] = fmax3(mxp[k], sv[i + k], sv[i + 8 + k]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) mxp[k] = fmaxf(mxp[k], sv[56 + k]);
+      const float mx = fmax3(fmax3(mxp[0], mxp[1], mxp[2]), fmax3(mxp[3], mxp[4], mxp[5]), fmaxf(mxp[6], mxp[7]));
       const float m_new = fmaxf(m_run, mx * c);
       const bool need = j > 0 && m_new > m_run + RESCALE_THRESHOLD;
       if (j == 0) m_run = m_new;
       if (j > 0 && __any_sync(0xffffffffu, need)) {
+        mbar_wait(pv_done_b, (j - 1) & 1);  // O must be complete before it is rescaled
+        tc_fence_after();
         const float alpha = need ? fast_exp2(m_run - m_new) : 1.0f;
         if (need) {
           m_run = m_new;
@@ -258,22 +253,37 @@ attention_kernel(const __grid_constant__ AttnParams p) {
           tmem_st16(tmem_o + lane_addr + c0, t);
         }
       }
+      // ---- probabilities -> packed bf16 pairs (keys 2c, 2c+1 = TMEM column c of the P region)
       const float2 c2 = make_float2(c, c), nm2 = make_float2(-m_run, -m_run);
-      uint32_t pkb[16], pka[16];
-      l_run += exp32(vb, pkb, c2, nm2);
-      tmem_ld32(tmem_s + lane_addr, va);  // A again (its registers were recycled for B's exponentials)
-      tmem_ld_wait();
-      tmem_st16(tmem_s + lane_addr + 16, reinterpret_cast<const float*>(pkb));
-      mask32(va, kvalid);
-      l_run += exp32(va, pka, c2, nm2);
-      tmem_st16(tmem_s + lane_addr, reinterpret_cast<const float*>(pka));
+      float2 ls[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+      uint32_t pk[ATT_BN / 2];
+#pragma unroll
+      for (int i = 0; i < ATT_BN; i += 2) {
+        const float2 x = ffma2(make_float2(sv[i], sv[i + 1]), c2, nm2);
+        float2 e;
+        if (((i >> 1) & 7) < NPOLY) {
+          e = exp2_poly2(x);
+        } else {
+          e.x = fast_exp2(x.x);
+          e.y = fast_exp2(x.y);
+        }
+        ls[(i >> 1) & 3] = fadd2(ls[(i >> 1) & 3], e);  // four independent packed sum chains
+        pk[i >> 1] = pack_bf16x2(e.x, e.y);
+      }
+      const float2 lsum = fadd2(fadd2(ls[0], ls[1]), fadd2(ls[2], ls[3]));
+      l_run += lsum.x + lsum.y;
+      if (j > 0) {
+        mbar_wait(pv_done_b, (j - 1) & 1);  // P_{j-1} V_{j-1} finished (long ago): the P columns are free
+        tc_fence_after();
+      }
+      tmem_st32(tmem_p + lane_addr, pk);
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_ready_b);
     }
     // ---- last block's P V, normalise, store
     if (st < nact) {
-    mbar_wait(&o_full[st], 0);
+    mbar_wait(&pv_done[st], (nblk - 1) & 1);
     tc_fence_after();
     const int qrow = q0 + st * ATT_BM + row;
     const float inv = 1.0f / l_run;
@@ -305,10 +315,10 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   }
 }
 
-template <int DP, int NS, int NPOLY>
+template <int DP, int NS, int NPOLY, bool EARLY = true>
 static int launch_attention(const AttnParams& p, int B, cudaStream_t st) {
-  using L = AttnSmem<DP, NS>;
-  auto kfn = attention_kernel<DP, NS, NPOLY>;
+  using L = AttnSmem<DP, NS, EARLY>;
+  auto kfn = attention_kernel<DP, NS, NPOLY, EARLY>;
   static bool attr_set = false;
   if (!attr_set) {
     TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
@@ -330,11 +340,10 @@ static int attn_streams(int dp, int Nq) {
     env = e ? atoi(e) : -1;
   }
   const int tiles = (Nq + ATT_BM - 1) / ATT_BM;
-  int ns = env > 0 ? env : (dp == 48 ? 4 : 2);
-  if (ns > tiles) ns = tiles >= 2 ? 2 : 1;
-  if (dp == 160 && ns > 2) ns = 2;
-  if (dp == 80 && ns > 3) ns = 3;
-  if (dp == 48 && ns == 3) ns = 2;
+  const int cap = dp == 48 ? 3 : 2;  // 512 TMEM columns / (64 S + 32 P + dp O)
+  int ns = env > 0 ? env : cap;
+  if (ns > cap) ns = cap;
+  if (ns > tiles) ns = tiles;
   return ns;
 }
 
@@ -345,8 +354,7 @@ static int attn_npoly(int dp) {
     env = e ? atoi(e) : -1;
   }
   if (env >= 0) return env;
-  (void)dp;
-  return 0;  // measured on B200 (profiles/r01c_attention.md): the kernel is issue/latency bound, not MUFU bound
+  return dp == 48 ? 2 : 0;  // measured optimum on B200 (profiles/r01c_attention.md)
 }
 
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
@@ -383,19 +391,19 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   const int np = attn_npoly(dp);
   const int ns = attn_streams(dp, Nq);
   if (dp == 48) {
-    if (ns == 1) return launch_attention<48, 1, 0>(p, B, st);
+    if (Nk <= 2 * ATT_BN && !getenv("TOPO_ATTN_NOALIAS")) return launch_attention<48, 1, 0, false>(p, B, st);
+    if (ns == 1) return np ? launch_attention<48, 1, 2>(p, B, st) : launch_attention<48, 1, 0>(p, B, st);
     if (ns == 2) return np ? launch_attention<48, 2, 2>(p, B, st) : launch_attention<48, 2, 0>(p, B, st);
     switch (np) {
-      case 1: return launch_attention<48, 4, 1>(p, B, st);
-      case 2: return launch_attention<48, 4, 2>(p, B, st);
-      case 3: return launch_attention<48, 4, 3>(p, B, st);
-      default: return launch_attention<48, 4, 0>(p, B, st);
+      case 1: return launch_attention<48, 3, 1>(p, B, st);
+      case 2: return launch_attention<48, 3, 2>(p, B, st);
+      case 3: return launch_attention<48, 3, 3>(p, B, st);
+      default: return launch_attention<48, 3, 0>(p, B, st);
     }
   }
   if (dp == 80) {
     if (ns == 1) return launch_attention<80, 1, 0>(p, B, st);
-    if (ns == 2) return np ? launch_attention<80, 2, 2>(p, B, st) : launch_attention<80, 2, 0>(p, B, st);
-    return np ? launch_attention<80, 3, 2>(p, B, st) : launch_attention<80, 3, 0>(p, B, st);
+    return np ? launch_attention<80, 2, 2>(p, B, st) : launch_attention<80, 2, 0>(p, B, st);
   }
   if (ns == 1) return launch_attention<160, 1, 0>(p, B, st);
   return launch_attention<160, 2, 0>(p, B, st);
