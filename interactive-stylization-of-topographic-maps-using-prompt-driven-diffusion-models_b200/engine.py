@@ -325,6 +325,11 @@ class PNet:
             self.mid_out = pack_conv1x1(net.middle_block_out[0], device)
             hb = [m for m in net.input_hint_block if isinstance(m, nn.Conv2d)]
             self.hint = [PConvIn(c, device) for c in hb]
+            # the last hint conv (256 -> model_channels at latent resolution, 41 % of the block's FLOPs) runs on the
+            # tensor-core implicit-GEMM kernel when its input width allows (C % 64 == 0)
+            last = hb[-1]
+            self.hint_last = pack_conv3x3(last, device) if (last.in_channels % 64 == 0 and last.kernel_size[0] == 3
+                                                            and last.stride[0] == 1) else None
         else:
             self.out_norm = pack_norm(net.out[0], device)
             self.out_conv = pack_conv3x3(net.out[2], device)
@@ -407,7 +412,12 @@ def run_up(u: PUp, x: torch.Tensor, B: int, H: int, W: int, dst: Dst = None) -> 
 def run_convin(c: PConvIn, x4: torch.Tensor, act: int = ACT_NONE, add: Optional[torch.Tensor] = None,
                out_fp32: bool = False) -> torch.Tensor:
     _count()
-    return ops.conv_direct(x4, c.w, c.b, c.cin, c.cout, c.k, c.stride, act=act, add=add, out_fp32=out_fp32)
+    Bn, H, W, _ = x4.shape
+    Ho, Wo = H // c.stride, W // c.stride
+    return _rec("conv_direct", 2.0 * Bn * Ho * Wo * c.cout * c.k * c.k * c.cin,
+                2.0 * (x4.numel() + Bn * Ho * Wo * c.cout * (2 if out_fp32 else 1)),
+                lambda: ops.conv_direct(x4, c.w, c.b, c.cin, c.cout, c.k, c.stride, act=act, add=add, out_fp32=out_fp32),
+                f"B{Bn} H{H} C{c.cin} N{c.cout} k{c.k} s{c.stride}")
 
 
 def run_layers(layers, h: torch.Tensor, B: int, H: int, W: int, emb, kv_iter, dst: Dst = None):
@@ -491,17 +501,30 @@ class TopoEngine:
         g = ops.nchw_to_nhwc(hint)
         _count()
         convs = self.cnet.hint
-        for i, c in enumerate(convs):
-            g = run_convin(c, g, act=ACT_SILU if i != len(convs) - 1 else ACT_NONE)
-        return g
+        for i, c in enumerate(convs[:-1]):
+            g = run_convin(c, g, act=ACT_SILU)
+        if self.cnet.hint_last is not None:
+            Bh, Hh, Wh, Ch = g.shape
+            if (Hh * Wh) % 128 == 0 or 128 % (Hh * Wh) == 0:
+                return conv3(g.view(Bh * Hh * Wh, Ch), Bh, Hh, Wh, self.cnet.hint_last).view(Bh, Hh, Wh, -1)
+        return run_convin(convs[-1], g, act=ACT_NONE)
 
     @torch.no_grad()
     def prepare(self, ctx: torch.Tensor, hint: Optional[torch.Tensor]) -> Prepared:
+        """``hint`` may hold fewer samples than ``ctx`` (Be = k * Bh): the batched CFG call passes the SAME control image
+        for the unconditional and the conditional half (vis_metrics.py:427-428), so the hint block runs once per tile
+        and its feature map is repeated along the batch."""
         Be = ctx.shape[0]
         ctx2 = ctx.reshape(-1, ctx.shape[-1]).to(BF16).contiguous()
         key = (ctx.data_ptr(), tuple(ctx.shape), None if hint is None else (hint.data_ptr(), tuple(hint.shape)))
-        return Prepared(key, self._kv(self.unet, ctx2, Be), self._kv(self.cnet, ctx2, Be),
-                        None if hint is None else self._hint(hint))
+        feat = None
+        if hint is not None:
+            feat = self._hint(hint)
+            if hint.shape[0] != Be:
+                if Be % hint.shape[0]:
+                    raise capi.TopoError(f"prepare: hint batch {hint.shape[0]} does not divide the context batch {Be}")
+                feat = feat.repeat(Be // hint.shape[0], 1, 1, 1)
+        return Prepared(key, self._kv(self.unet, ctx2, Be), self._kv(self.cnet, ctx2, Be), feat)
 
     def _time(self, net: PNet, t: torch.Tensor) -> torch.Tensor:
         e = ops.timestep_embedding(t, net.mc)
@@ -627,7 +650,7 @@ class PVAttn:
             sl = slice(b * N, (b + 1) * N)
             vT = gemm(self.vW, Lin(hn[sl], None))                       # [C, N] = Wv hn^T  (v without bias, transposed)
             s = gemm(q[sl], Lin(k[sl], None))                           # [N, N]
-            p = ops.softmax_rows(s, C ** -0.5)
+            p = _rec("softmax_rows", 0.0, 4.0 * s.numel(), lambda: ops.softmax_rows(s, C ** -0.5), f"N{N}")
             _count()
             gemm(p, Lin(vT, self.vb), out=o[sl])
         return gemm(o, self.proj, res=x)
@@ -665,7 +688,7 @@ class PVae:
             for rb in blocks:
                 h = rb.run(h, B, H, W)
             if up is not None:
-                y = ops.upsample2x(h.view(B, H, W, -1))
+                y = _rec("upsample2x", 0.0, 2.0 * 5 * h.numel(), lambda: ops.upsample2x(h.view(B, H, W, -1)), f"B{B} H{H} C{h.shape[1]}")
                 _count()
                 H, W = 2 * H, 2 * W
                 h = conv3(y.view(B * H * W, -1), B, H, W, up)
@@ -673,7 +696,7 @@ class PVae:
         img = run_convin(self.conv_out, h.view(B, H, W, -1), out_fp32=True)
         _count()
         if u8:  # evaluateCN.py:101-103: *127.5+127.5, clip, truncate → uint8 HWC, fused before the gather
-            return ops.tile_to_u8(img)
+            return _rec("tile_to_u8", 0.0, 5.0 * img.numel(), lambda: ops.tile_to_u8(img))
         return ops.nhwc_to_nchw(img)
 
 
@@ -688,13 +711,15 @@ class GraphedModel:
     encoded on the host at capture time and baked into the graph as kernel parameters."""
 
     def __init__(self, eng: TopoEngine, Be: int, lat_hw: Tuple[int, int], ctx_shape: Tuple[int, int],
-                 hint_hw: Optional[Tuple[int, int]], control_scales: Sequence[float], only_mid_control: bool):
+                 hint_hw: Optional[Tuple[int, int]], control_scales: Sequence[float], only_mid_control: bool,
+                 hint_batch: Optional[int] = None):
         dev = eng.device
         self.eng = eng
         self.x = torch.zeros(Be, 4, *lat_hw, device=dev)
         self.t = torch.zeros(Be, device=dev)
         self.ctx = torch.zeros(Be, *ctx_shape, device=dev)
-        self.hint = None if hint_hw is None else torch.zeros(Be, 3, *hint_hw, device=dev)
+        # hint_batch < Be: the CFG halves share their control images (see TopoEngine.prepare)
+        self.hint = None if hint_hw is None else torch.zeros(hint_batch or Be, 3, *hint_hw, device=dev)
         scales = [float(s) for s in control_scales]
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -728,12 +753,13 @@ class GraphedModel:
         return self.eps
 
 
-def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control) -> GraphedModel:
-    key = (Be, tuple(lat_hw), tuple(ctx_shape), None if hint_hw is None else tuple(hint_hw),
+def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control,
+             hint_batch=None) -> GraphedModel:
+    key = (Be, hint_batch or Be, tuple(lat_hw), tuple(ctx_shape), None if hint_hw is None else tuple(hint_hw),
            tuple(float(s) for s in control_scales), bool(only_mid_control))
     cache = self.__dict__.setdefault("_graphs", {})
     if key not in cache:
-        cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control)
+        cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control, hint_batch)
     return cache[key]
 
 

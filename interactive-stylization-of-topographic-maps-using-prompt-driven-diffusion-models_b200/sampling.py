@@ -72,7 +72,15 @@ class DDIMSampler:
             return ctx, hint
 
         if cfg and not self.hacked:
-            conds = [_pack(self._cat_cond(unconditional_conditioning, conditioning))]
+            uh, ch = unconditional_conditioning.get("c_concat"), conditioning.get("c_concat")
+            shared = (uh is not None and ch is not None and len(uh) == len(ch)
+                      and all(a is b for a, b in zip(uh, ch)))  # same control images for both CFG halves
+            if shared:
+                ctx_u, _ = _pack({"c_crossattn": unconditional_conditioning["c_crossattn"]})
+                ctx_c, hint = _pack(conditioning)
+                conds = [(torch.cat([ctx_u, ctx_c]), hint)]
+            else:
+                conds = [_pack(self._cat_cond(unconditional_conditioning, conditioning))]
         elif cfg:
             conds = [_pack(unconditional_conditioning), _pack(conditioning)]  # eps buffer layout is [uncond ; cond]
         else:
@@ -85,7 +93,7 @@ class DDIMSampler:
             for ctx, hint in conds:
                 # the hacked variant needs two sets of static buffers: distinct graphs for the two branches
                 g = eng.graphed(ctx.shape[0], (H, W), tuple(ctx.shape[1:]), None if hint is None else tuple(hint.shape[2:]),
-                                scales, omc) if len(conds) == 1 else GraphedModel(
+                                scales, omc, None if hint is None else hint.shape[0]) if len(conds) == 1 else GraphedModel(
                                     eng, ctx.shape[0], (H, W), tuple(ctx.shape[1:]),
                                     None if hint is None else tuple(hint.shape[2:]), scales, omc)
                 g.set_cond(ctx, hint)

@@ -14,7 +14,7 @@ model = synth.build_model("ctrlora", control_lora_rank=16).to(dev)
 eng = model.engine()
 hints, ctx, xT = synth.make_hint(T, 512).to(dev), synth.make_ctx(T).to(dev), synth.make_xT(T, 64).to(dev)
 c2 = torch.cat([torch.zeros_like(ctx), ctx]); h2 = torch.cat([hints, hints]); x2 = torch.cat([xT, xT])
-g = eng.graphed(2 * T, (64, 64), tuple(ctx.shape[1:]), (512, 512), model.control_scales, False)
+g = eng.graphed(2 * T, (64, 64), tuple(ctx.shape[1:]), (512, 512), model.control_scales, False, T)
 
 
 def ev():
@@ -32,7 +32,7 @@ def timed(fn, n=3):
 
 
 g.x.copy_(x2); g.t.fill_(501.0)
-t_prep = timed(lambda: g.set_cond(c2, h2))
+t_prep = timed(lambda: g.set_cond(c2, hints))
 t_step = timed(lambda: g.step(), 5)
 t_31 = timed(lambda: [g.step() for _ in range(31)], 2)
 z = torch.randn(T, 4, 64, 64, device=dev)
