@@ -673,6 +673,18 @@ class PVae:
             self.levels.append((blocks, up))
         self.norm_out = pack_norm(dec.norm_out, device)
         self.conv_out = PConvIn(dec.conv_out, device)
+        # conv_out (128 -> 3 at 512x512) as a tensor-core implicit GEMM with the 3 output channels zero-padded to the
+        # smallest UMMA N (16): the direct kernel spent 31.8 ms of a 87 ms decode here (profiles/r01d_stage.txt)
+        co = dec.conv_out
+        self.conv_out_tc = None
+        if co.in_channels % 64 == 0 and co.kernel_size[0] == 3 and co.out_channels <= 16:
+            w = torch.zeros(16, co.in_channels, 3, 3, device=device)
+            w[:co.out_channels] = co.weight.detach().to(device).float()
+            b = torch.zeros(16, device=device)
+            if co.bias is not None:
+                b[:co.out_channels] = co.bias.detach().to(device).float()
+            self.conv_out_tc = Lin(ops.conv3x3_weight(w), b)
+            self.out_ch = co.out_channels
 
     def decode(self, z: torch.Tensor, u8: bool = False) -> torch.Tensor:
         B, _, H, W = z.shape
@@ -693,7 +705,10 @@ class PVae:
                 H, W = 2 * H, 2 * W
                 h = conv3(y.view(B * H * W, -1), B, H, W, up)
         h = gn(h, B, self.norm_out, True)
-        img = run_convin(self.conv_out, h.view(B, H, W, -1), out_fp32=True)
+        if self.conv_out_tc is not None and W % 128 == 0:
+            img = conv3(h, B, H, W, self.conv_out_tc, out_fp32=True).view(B, H, W, 16)[..., :self.out_ch]
+        else:
+            img = run_convin(self.conv_out, h.view(B, H, W, -1), out_fp32=True)
         _count()
         if u8:  # evaluateCN.py:101-103: *127.5+127.5, clip, truncate → uint8 HWC, fused before the gather
             return _rec("tile_to_u8", 0.0, 5.0 * img.numel(), lambda: ops.tile_to_u8(img))

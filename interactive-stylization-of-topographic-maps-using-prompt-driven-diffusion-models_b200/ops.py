@@ -267,7 +267,7 @@ def nhwc_to_nchw(x: torch.Tensor) -> torch.Tensor:
     """bf16/fp32 NHWC -> fp32 NCHW."""
     Bn, H, Wd, Cc = x.shape
     y = torch.empty(Bn, Cc, H, Wd, dtype=torch.float32, device=x.device)
-    capi.check(capi.load_library().topo_nhwc_to_nchw_f32(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), Cc,
+    capi.check(capi.load_library().topo_nhwc_to_nchw_f32(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), x.stride(-2),
                                                          y.data_ptr(), Bn, Cc, H * Wd, capi.stream()),
                "topo_nhwc_to_nchw_f32")
     return y
@@ -300,8 +300,9 @@ def add(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
 def tile_to_u8(x: torch.Tensor) -> torch.Tensor:
     """NHWC [-1,1] (bf16 or fp32) -> uint8 NHWC (BaseModel/evaluateCN.py:101-103)."""
     Cc = x.shape[-1]
+    ld = x.stride(-2)  # a channel slice of a wider pixel-major buffer is fine (pixels must be evenly strided)
     y = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
-    capi.check(capi.load_library().topo_tile_to_u8(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), Cc,
+    capi.check(capi.load_library().topo_tile_to_u8(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), ld,
                                                    y.data_ptr(), x.numel() // Cc, Cc, capi.stream()), "topo_tile_to_u8")
     return y
 
