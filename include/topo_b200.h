@@ -114,9 +114,12 @@ int topo_timestep_embedding(topo_handle_t h, const float* t, void* emb, int B, i
 int topo_ddim_step(topo_handle_t h, const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w,
                    float a_t, float a_prev, float sigma, const float* noise, void* stream);
 /* direct convolution for the narrow layers (C_in not a multiple of 64: conv_in, the hint block, VAE conv_in):
- *   x NHWC [B,H,W,Cin] bf16, w bf16 [Cout, kh*kw*Cin], out NHWC [B,Ho,Wo,Cout]; optional SiLU; out += add if add  */
+ *   x NHWC [B,H,W,Cin] bf16, w bf16 [Cout, kh*kw*Cin], out NHWC [B,Ho,Wo,Cout]; optional SiLU; out += add if add.
+ *   pad_lo = zero rows/columns before the image (-1: ksize/2, the symmetric convolution).  pad_lo = 0 with ksize 3,
+ *   stride 2 is diffusers' Downsample2D(padding=0): F.pad(x, (0,1,0,1)) then a stride-2 conv
+ *   (LoRA_modified/models.py:597-601, downsample_padding=0 at :709,758).                                            */
 int topo_conv_direct(topo_handle_t h, const void* x, int x_ld, const void* w, const float* bias, void* out,
-                     int out_ld, int B, int H, int W, int Cin, int Cout, int ksize, int stride, int act,
+                     int out_ld, int B, int H, int W, int Cin, int Cout, int ksize, int stride, int pad_lo, int act,
                      const void* add, int add_ld, int out_fp32, void* stream);
 /* layout / resampling helpers */
 int topo_nchw_f32_to_nhwc_bf16(topo_handle_t h, const float* x, void* y, int B, int C, int HW, int y_ld, void* stream);

@@ -72,8 +72,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_zeroconv_residual.argtypes = [vp, vp, i32, vp, vp, f32, vp, i32, vp, i32, i32, i32, i32, vp]
     lib.topo_timestep_embedding.argtypes = [vp, vp, vp, i32, i32, vp]
     lib.topo_ddim_step.argtypes = [vp, vp, vp, vp, i64, i32, f32, f32, f32, f32, vp, vp]
-    lib.topo_conv_direct.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp, i32,
-                                     i32, vp]
+    lib.topo_conv_direct.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp,
+                                     i32, i32, vp]
     lib.topo_nchw_f32_to_nhwc_bf16.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]
     lib.topo_nhwc_to_nchw_f32.argtypes = [vp, vp, i32, i32, vp, i32, i32, i32, vp]
     lib.topo_upsample2x.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]

@@ -85,8 +85,8 @@ int timestep_embedding_dispatch(const float* t, void* emb, int B, int dim, cudaS
 int ddim_step_dispatch(const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w, float a_t,
                        float a_prev, float sigma, const float* noise, cudaStream_t st);
 int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bias, void* out, int out_ld, int B, int H,
-                         int W, int Cin, int Cout, int ksize, int stride, int act, const void* add, int add_ld,
-                         int out_fp32, cudaStream_t st);
+                         int W, int Cin, int Cout, int ksize, int stride, int pad_lo, int act, const void* add,
+                         int add_ld, int out_fp32, cudaStream_t st);
 int nchw_to_nhwc_dispatch(const float* x, void* y, int B, int C, int HW, int y_ld, cudaStream_t st);
 int nhwc_to_nchw_dispatch(const void* x, int x_is_f32, int x_ld, float* y, int B, int C, int HW, cudaStream_t st);
 int upsample2x_dispatch(const void* x, int x_ld, void* y, int y_ld, int B, int H, int W, int C, cudaStream_t st);
@@ -237,11 +237,11 @@ int topo_ddim_step(topo_handle_t h, const float* x, const float* eps, float* x_o
 }
 
 int topo_conv_direct(topo_handle_t h, const void* x, int x_ld, const void* w, const float* bias, void* out, int out_ld,
-                     int B, int H, int W, int Cin, int Cout, int ksize, int stride, int act, const void* add,
-                     int add_ld, int out_fp32, void* stream) {
+                     int B, int H, int W, int Cin, int Cout, int ksize, int stride, int pad_lo, int act,
+                     const void* add, int add_ld, int out_fp32, void* stream) {
   H_CHECK(h);
-  return conv_direct_dispatch(x, x_ld, w, bias, out, out_ld, B, H, W, Cin, Cout, ksize, stride, act, add, add_ld,
-                              out_fp32, ST(stream));
+  return conv_direct_dispatch(x, x_ld, w, bias, out, out_ld, B, H, W, Cin, Cout, ksize, stride, pad_lo, act, add,
+                              add_ld, out_fp32, ST(stream));
 }
 
 int topo_nchw_f32_to_nhwc_bf16(topo_handle_t h, const float* x, void* y, int B, int C, int HW, int y_ld, void* stream) {

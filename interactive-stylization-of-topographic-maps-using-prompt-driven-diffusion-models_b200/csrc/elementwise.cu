@@ -60,8 +60,8 @@ int ddim_step_dispatch(const float* x, const float* eps, float* x_out, int64_t n
 __global__ void __launch_bounds__(256) conv_direct_kernel(const bf16* __restrict__ x, int x_ld, const bf16* __restrict__ w,
                                                          const float* __restrict__ bias, void* __restrict__ out,
                                                          int out_ld, int B, int H, int W, int Cin, int Cout, int ks,
-                                                         int stride, int act, const bf16* __restrict__ add, int add_ld,
-                                                         int out_fp32) {
+                                                         int stride, int pad, int act, const bf16* __restrict__ add,
+                                                         int add_ld, int out_fp32) {
   const int Ho = (H + 2 * (ks / 2) - ks) / stride + 1;
   const int Wo = (W + 2 * (ks / 2) - ks) / stride + 1;
   const int cgs = (Cout + 7) >> 3;
@@ -78,7 +78,6 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const bf16* __restrict
   float acc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) acc[i] = (bias && co + i < Cout) ? bias[co + i] : 0.f;
-  const int pad = ks / 2;
   for (int ky = 0; ky < ks; ++ky) {
     const int hi = ho * stride + ky - pad;
     if (hi < 0 || hi >= H) continue;
@@ -115,16 +114,19 @@ __global__ void __launch_bounds__(256) conv_direct_kernel(const bf16* __restrict
 }
 
 int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bias, void* out, int out_ld, int B, int H,
-                         int W, int Cin, int Cout, int ksize, int stride, int act, const void* add, int add_ld,
-                         int out_fp32, cudaStream_t st) {
+                         int W, int Cin, int Cout, int ksize, int stride, int pad_lo, int act, const void* add,
+                         int add_ld, int out_fp32, cudaStream_t st) {
   TOPO_CHECK(ksize == 1 || ksize == 3, TOPO_E_INVAL, "conv_direct: ksize must be 1 or 3");
   TOPO_CHECK(stride == 1 || stride == 2, TOPO_E_INVAL, "conv_direct: stride must be 1 or 2");
-  const int pad = ksize / 2;
+  const int pad = ksize / 2;  // output extent: total padding 2 * (ksize / 2) (equal for pad_lo = 0 and even H, W at stride 2)
+  TOPO_CHECK(pad_lo >= -1 && pad_lo <= pad, TOPO_E_INVAL, "conv_direct: pad_lo must be -1 (symmetric) or in [0, %d]", pad);
+  TOPO_CHECK(pad_lo < 0 || pad_lo == pad || (stride == 2 && H % 2 == 0 && W % 2 == 0), TOPO_E_INVAL,
+             "conv_direct: asymmetric padding needs stride 2 and even H, W");
   const int Ho = (H + 2 * pad - ksize) / stride + 1, Wo = (W + 2 * pad - ksize) / stride + 1;
   const int64_t total = (int64_t)B * Ho * Wo * ((Cout + 7) / 8);
   conv_direct_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
       reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<const bf16*>(w), bias, out, out_ld, B, H, W, Cin, Cout,
-      ksize, stride, act, reinterpret_cast<const bf16*>(add), add_ld, out_fp32);
+      ksize, stride, pad_lo < 0 ? pad : pad_lo, act, reinterpret_cast<const bf16*>(add), add_ld, out_fp32);
   TOPO_CUDA(cudaGetLastError());
   return 0;
 }

@@ -239,8 +239,9 @@ def ddim_step(x: torch.Tensor, eps: torch.Tensor, cfg: bool, w: float, a_t: floa
 
 def conv_direct(x: torch.Tensor, w_t: torch.Tensor, bias: Optional[torch.Tensor], Cin: int, Cout: int, ksize: int,
                 stride: int, act: int = ACT_NONE, add: Optional[torch.Tensor] = None, out_fp32=False,
-                out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """x NHWC bf16 [B,H,W,Cin]; w_t from ``conv_direct_weight``; returns NHWC [B,Ho,Wo,Cout]."""
+                out: Optional[torch.Tensor] = None, pad_lo: int = -1) -> torch.Tensor:
+    """x NHWC bf16 [B,H,W,Cin]; w_t from ``conv_direct_weight``; returns NHWC [B,Ho,Wo,Cout].  ``pad_lo=0`` with
+    stride 2 is diffusers' ``Downsample2D(padding=0)`` (zero row/column appended after the image only)."""
     Bn, H, Wd, _ = x.shape
     pad = ksize // 2
     Ho, Wo = (H + 2 * pad - ksize) // stride + 1, (Wd + 2 * pad - ksize) // stride + 1
@@ -248,7 +249,7 @@ def conv_direct(x: torch.Tensor, w_t: torch.Tensor, bias: Optional[torch.Tensor]
         out = torch.empty(Bn, Ho, Wo, Cout, dtype=torch.float32 if out_fp32 else BF16, device=x.device)
     capi.check(capi.load_library().topo_conv_direct(
         capi.handle(), x.data_ptr(), x.shape[-1], w_t.data_ptr(), capi.ptr(bias), out.data_ptr(), out.shape[-1], Bn, H,
-        Wd, Cin, Cout, ksize, stride, act, capi.ptr(add), 0 if add is None else add.shape[-1], int(out_fp32),
+        Wd, Cin, Cout, ksize, stride, pad_lo, act, capi.ptr(add), 0 if add is None else add.shape[-1], int(out_fp32),
         capi.stream()), "topo_conv_direct")
     return out
 

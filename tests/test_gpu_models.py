@@ -1,0 +1,176 @@
+"""-m gpu: the diffusers-processor LoRA attention and the ControlLoRA pyramid (topo_b200/models.py, mirror of
+LoRA_modified/models.py) through the C ABI vs the fp32 oracle (oracle/models_oracle.py) on the same weights / inputs.
+Tolerances: attention layer outputs are bf16 chains of 4-8 GEMMs + one flash attention -> 2e-2 of the tensor's max
+magnitude and cosine >= 0.999; the pyramid stacks up to 14 GroupNorm/conv stages in bf16 -> 4e-2 / cosine >= 0.999."""
+import pytest
+import torch
+
+from gpu_util import assert_close
+
+pytestmark = pytest.mark.gpu
+C, HEADS, D, CTX, N, B = 320, 8, 40, 768, 256, 2
+
+
+def _mods():
+    from topo_b200 import models as M
+    from oracle import models_oracle as O
+    return M, O
+
+
+def _randomize(mod, seed):
+    """LoRA `up` matrices are zero-initialised (parity would be vacuous): give every parameter a non-trivial value."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in mod.named_parameters():
+            if name.endswith("up.weight"):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.05)
+            elif name.endswith("down.weight"):
+                p.copy_(torch.randn(p.shape, generator=g) * p.shape[1] ** -0.5)
+    return mod
+
+
+def _attn(M, cross, seed=0):
+    torch.manual_seed(seed)
+    return M.CrossAttention(C, CTX if cross else None, HEADS, D).cuda()
+
+
+def _inputs(cross, seed=1):
+    g = torch.Generator().manual_seed(seed)
+    h = torch.randn(B, N, C, generator=g).cuda()
+    e = torch.randn(B, 77, CTX, generator=g).cuda() if cross else None
+    ctrl = torch.randn(B, C, 16, 16, generator=g).cuda()
+    return h, e, ctrl
+
+
+def _check(attn, proc, h, e, O, what, scale=1.0):
+    attn.set_processor(proc)
+    got = attn(h, encoder_hidden_states=e, scale=scale)
+    ref = O.processor_call(attn, proc, h, e, scale)
+    assert got.shape == ref.shape and got.dtype == h.dtype
+    cos = torch.nn.functional.cosine_similarity(got.flatten().float(), ref.flatten(), dim=0).item()
+    print(f"[parity] {what}: cosine={cos:.6f}")
+    assert cos >= 0.999
+    assert_close(got, ref, 2e-2, what)
+
+
+@pytest.mark.parametrize("cross", [False, True])
+@pytest.mark.parametrize("post_add", [False, True])
+def test_lora_processor(cross, post_add):
+    M, O = _mods()
+    attn = _attn(M, cross)
+    proc = _randomize(M.LoRACrossAttnProcessor(C, CTX if cross else None, rank=4, post_add=post_add), 3).cuda()
+    h, e, _ = _inputs(cross)
+    _check(attn, proc, h, e, O, f"LoRACrossAttnProcessor cross={cross} post_add={post_add}", scale=0.8)
+
+
+def test_lora_processor_skips_and_default():
+    M, O = _mods()
+    attn = _attn(M, True)
+    h, e, _ = _inputs(True)
+    ref0 = O.processor_call(attn, M.LoRACrossAttnProcessor(C, CTX, rank=4).cuda(), h, e)  # zero `up`: plain attention
+    assert_close(attn(h, encoder_hidden_states=e), ref0, 2e-2, "default CrossAttnProcessor")
+    proc = _randomize(M.LoRACrossAttnProcessor(C, CTX, rank=8, key_states_skipped=True), 4).cuda()
+    assert not hasattr(proc, "to_k_lora")
+    proc.skip_output_states(True)
+    _check(attn, proc, h, e, O, "LoRACrossAttnProcessor k absent, out muted")
+
+
+@pytest.mark.parametrize("concat_hidden,post_add", [(False, False), (True, False), (False, True)])
+def test_control_processor_v1(concat_hidden, post_add):
+    M, O = _mods()
+    attn = _attn(M, True)
+    h, e, ctrl = _inputs(True)
+    proc = _randomize(M.ControlLoRACrossAttnProcessor(C, CTX, rank=4, control_rank=8, concat_hidden=concat_hidden,
+                                                      post_add=post_add), 5).cuda()
+    assert proc.control_self_add is False   # reference :182
+    c1, c2 = ctrl.clone(), ctrl.clone()
+    proc.inject_control_states(c1)
+    assert proc.control_states is c1        # alias, reference :198-199
+    attn.set_processor(proc)
+    got = attn(h, encoder_hidden_states=e, scale=0.9)
+    assert proc.control_states.shape == (B, 256, C)   # flattened map cached back, reference :203-206
+    proc.inject_control_states(c2)
+    ref = O.processor_call(attn, proc, h, e, 0.9)
+    assert_close(got, ref, 2e-2, f"ControlLoRACrossAttnProcessor concat={concat_hidden} post_add={post_add}")
+
+
+def test_control_processor_v1_stacks():
+    M, O = _mods()
+    attn = _attn(M, False)
+    h, _, ctrl = _inputs(False)
+    proc = _randomize(M.ControlLoRACrossAttnProcessor(C, None, rank=4), 6).cuda()
+    pre = _randomize(M.LoRACrossAttnProcessor(C, None, rank=4, post_add=True), 7).cuda()
+    post = _randomize(M.ControlLoRACrossAttnProcessor(C, None, rank=16, concat_hidden=True), 8).cuda()
+    proc.inject_pre_lora(pre)
+    proc.inject_post_lora(post)
+    for p in (proc, post):
+        p.inject_control_states(ctrl.clone())
+    attn.set_processor(proc)
+    got = attn(h)
+    for p in (proc, post):
+        p.inject_control_states(ctrl.clone())
+    assert_close(got, O.processor_call(attn, proc, h, None, 1.0), 2e-2, "ControlLoRA v1 with pre/post stacks")
+
+
+def test_control_processor_v2():
+    M, O = _mods()
+    attn = _attn(M, True)
+    h, e, ctrl = _inputs(True)
+    proc = _randomize(M.ControlLoRACrossAttnProcessorV2(C, CTX, rank=4, control_rank=8), 9).cuda()
+    pre = _randomize(M.ControlLoRACrossAttnProcessorV2(C, CTX, rank=4), 10).cuda()
+    proc.inject_pre_lora(pre)
+    assert proc.key_states_skipped and proc.value_states_skipped and not hasattr(proc, "to_k_lora")
+    for p in (proc, pre):
+        p.inject_control_states(ctrl.clone())
+    attn.set_processor(proc)
+    got = attn(h, encoder_hidden_states=e)
+    for p in (proc, pre):
+        p.inject_control_states(ctrl.clone())
+    assert_close(got, O.processor_call(attn, proc, h, e, 1.0), 2e-2, "ControlLoRACrossAttnProcessorV2 + pre V2")
+
+
+def test_control_batch_repeat_and_process_control_states():
+    M, O = _mods()
+    h, _, ctrl = _inputs(False)
+    proc = _randomize(M.ControlLoRACrossAttnProcessor(C, None, rank=4, concat_hidden=True), 11).cuda()
+    proc.inject_control_states(ctrl[:1].clone())          # one control image for a batch of two (reference :209-212)
+    got = proc.process_control_states(h, 0.5)
+    proc.inject_control_states(ctrl[:1].clone())
+    assert_close(got, O.process_control_states(proc, h, 0.5), 2e-2, "process_control_states b1 != b2")
+
+
+def test_protocol_helpers():
+    M, O = _mods()
+    attn = _attn(M, False)
+    g = torch.Generator().manual_seed(2)
+    q, k = torch.randn(2 * HEADS, 64, D, generator=g).cuda(), torch.randn(2 * HEADS, 77, D, generator=g).cuda()
+    p = attn.get_attention_scores(q, k)
+    ref = torch.softmax(torch.bmm(q.bfloat16().float(), k.bfloat16().float().transpose(1, 2)) * attn.scale, -1)
+    assert_close(p, ref, 2e-2, "get_attention_scores")
+    t = torch.randn(2, 64, C, generator=g).cuda()
+    assert torch.equal(attn.batch_to_head_dim(attn.head_to_batch_dim(t)), t)
+    assert torch.equal(attn.head_to_batch_dim(t), O._heads(t, HEADS))
+    from topo_b200.capi import TopoError
+    with pytest.raises(TopoError):
+        attn.prepare_attention_mask(torch.ones(2, 64, device="cuda"), 64)
+    assert attn.prepare_attention_mask(None, 64) is None
+
+
+def test_control_lora_pyramid():
+    M, O = _mods()
+    torch.manual_seed(0)
+    model = M.ControlLoRA().cuda()
+    g = torch.Generator().manual_seed(3)
+    x = torch.rand(1, 3, 512, 512, generator=g).cuda()
+    assert model(x) is None                               # reference :832-868 (return_dict=True falls through)
+    outs = model(x, return_dict=False)
+    ref = O.control_lora_forward(model, x)
+    assert [tuple(o.shape[1:]) for o in outs] == [(320, 64, 64), (640, 32, 32), (1280, 16, 16), (1280, 8, 8)]
+    for lvl, layers in enumerate(model.lora_layers):
+        assert all(l.control_states is outs[lvl] for l in layers)   # every processor of the level aliases the same map
+    assert [len(l) for l in model.lora_layers] == [10, 10, 10, 2]
+    for i, (a, b) in enumerate(zip(outs, ref)):
+        cos = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
+        print(f"[parity] ControlLoRA level {i}: cosine={cos:.6f}")
+        assert cos >= 0.999
+        assert_close(a, b, 4e-2, f"ControlLoRA control map {i}")

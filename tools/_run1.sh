@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; echo "stage rc=$?"; head -12 gpurun_out/stage.log
-timeout 900 python -m pytest tests/test_gpu_e2e.py -m gpu -x -q > gpurun_out/e2e.log 2>&1; echo "e2e rc=$?"; tail -3 gpurun_out/e2e.log
+timeout 600 python -m pytest tests/test_gpu_models.py -m gpu -q -s -x > gpurun_out/models.log 2>&1; echo "models rc=$?"; grep -E "parity|Error|error|assert|passed|failed" gpurun_out/models.log | tail -40
