@@ -38,6 +38,8 @@ int topo_version(void);
 /* activation selectors for topo_linear_t.act */
 #define TOPO_ACT_NONE 0
 #define TOPO_ACT_SILU 1
+#define TOPO_ACT_GELU 3  /* exact-erf GELU (BERT intermediate) */
+#define TOPO_ACT_RELU 4  /* text-adapter MLP */
 #define TOPO_ACT_GEGLU 2 /* rows of W are tile-interleaved [t/2 values | t/2 gates] per t = topo_geglu_tile(N) rows; output has N/2 columns */
 
 /* One output segment of a projection:   out = alpha * (x W^T + s (x A^T) B^T + bias + rowbias) + res
@@ -87,6 +89,16 @@ int topo_conv3x3(topo_handle_t h, const void* x, int B, int H, int W, int C, int
  *     attention.py; subclassed at LoRA_modified/attention_lora.py:35,75).                            */
 int topo_attention(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq,
                    int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, void* stream);
+/* Same with a per-sample key length: keys >= kv_len[b] (device int32 [B]) are masked and whole key blocks past the
+ *     length are skipped.  This is the attention_mask of the BERT prompt encoder for right-padded prompts
+ *     (tokenizer(padding="max_length"), LoRA_modified/multiseg_19prompts_batch1_shuffle_ctrlora.py:175-184);
+ *     dp = 64 serves BERT-base's 12 x 64 heads.                                                              */
+int topo_attention_varlen(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads,
+                          int Nq, int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len,
+                          void* stream);
+/* BERT embeddings: y[b,t,:] = word[ids[b,t]] + pos[t] + type[0]  (bf16 out, fp32 tables); followed by topo_layernorm */
+int topo_embed_sum(topo_handle_t h, const int* ids, const float* word, const float* pos, const float* type0, void* y,
+                   int B, int T, int C, int vocab, void* stream);
 
 /* (d) y = silu?(GroupNorm(x; G groups, eps)) on NHWC x [B, HW, C] (row stride x_ld / y_ld elements);
  *     gamma/beta fp32 [C]; statistics in fp32 (GroupNorm32, upstream ldm util.py).

@@ -32,6 +32,7 @@ constexpr int ATT_BN = 64;   // keys per block
 struct alignas(64) AttnParams {
   CUtensorMap tm_q, tm_k, tm_v;  // 3-D (cols, rows, batch); box (64, 128, 1) for Q, (64, 64, 1) for K/V; SW128
   bf16* o;
+  const int* kv_len;             // optional [B]: keys >= kv_len[b] are masked (right-padded prompts); nullptr = all Nk
   int Nq, Nk, heads, ldo;
   float scale_log2e;
 };
@@ -88,7 +89,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   const int q0 = blockIdx.x * (ATT_BM * NS);
   const int head = blockIdx.y;
   const int b = blockIdx.z;
-  const int nblk = (p.Nk + ATT_BN - 1) / ATT_BN;
+  const int Nk = p.kv_len ? max(1, min(p.Nk, __ldg(p.kv_len + b))) : p.Nk;  // whole blocks past the length are skipped
+  const int nblk = (Nk + ATT_BN - 1) / ATT_BN;
   const int col0 = head * DP;
   const int nact = min(NS, (p.Nq - q0 + ATT_BM - 1) / ATT_BM);  // streams with at least one query row
 
@@ -208,7 +210,7 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     constexpr float RESCALE_THRESHOLD = 8.0f;
 
     for (int j = 0; j < nblk_st; ++j) {
-      const int kvalid = min(ATT_BN, p.Nk - j * ATT_BN);
+      const int kvalid = min(ATT_BN, Nk - j * ATT_BN);
       mbar_wait(s_full_b, j & 1);
       tc_fence_after();
       float sv[ATT_BN];
@@ -340,7 +342,7 @@ static int attn_streams(int dp, int Nq) {
     env = e ? atoi(e) : -1;
   }
   const int tiles = (Nq + ATT_BM - 1) / ATT_BM;
-  const int cap = dp == 48 ? 3 : 2;  // 512 TMEM columns / (64 S + 32 P + dp O)
+  const int cap = dp <= 64 ? 3 : 2;  // 512 TMEM columns / (64 S + 32 P + dp O)
   int ns = env > 0 ? env : cap;
   if (ns > cap) ns = cap;
   if (ns > tiles) ns = tiles;
@@ -358,8 +360,9 @@ static int attn_npoly(int dp) {
 }
 
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
-                       int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t st) {
-  TOPO_CHECK(dp == 48 || dp == 80 || dp == 160, TOPO_E_INVAL, "attention: padded head dim must be 48, 80 or 160 (got %d)", dp);
+                       int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len, cudaStream_t st) {
+  TOPO_CHECK(dp == 48 || dp == 64 || dp == 80 || dp == 160, TOPO_E_INVAL,
+             "attention: padded head dim must be 48, 64, 80 or 160 (got %d)", dp);
   TOPO_CHECK(((ldq | ldk | ldv | ldo) & 7) == 0, TOPO_E_INVAL, "attention: leading dims must be multiples of 8");
   TOPO_CHECK(B > 0 && heads > 0 && Nq > 0 && Nk > 0, TOPO_E_INVAL, "attention: empty problem");
   AttnParams p;
@@ -383,6 +386,7 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
     if (rc) return rc;
   }
   p.o = reinterpret_cast<bf16*>(o);
+  p.kv_len = kv_len;
   p.Nq = Nq;
   p.Nk = Nk;
   p.heads = heads;
@@ -400,6 +404,11 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
       case 3: return launch_attention<48, 3, 3>(p, B, st);
       default: return launch_attention<48, 3, 0>(p, B, st);
     }
+  }
+  if (dp == 64) {  // BERT-base heads (12 x 64) of the text conditioning producer
+    if (ns == 1) return launch_attention<64, 1, 0>(p, B, st);
+    if (ns == 2) return launch_attention<64, 2, 0>(p, B, st);
+    return launch_attention<64, 3, 0>(p, B, st);
   }
   if (dp == 80) {
     if (ns == 1) return launch_attention<80, 1, 0>(p, B, st);

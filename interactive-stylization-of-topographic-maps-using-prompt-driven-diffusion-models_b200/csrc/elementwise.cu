@@ -131,6 +131,36 @@ int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bi
   return 0;
 }
 
+// ---- BERT embedding sum: one thread per 4 channels of one token ---------------------------------------
+__global__ void __launch_bounds__(256) embed_sum_kernel(const int* __restrict__ ids, const float* __restrict__ word,
+                                                       const float* __restrict__ pos, const float* __restrict__ type0,
+                                                       bf16* __restrict__ y, int T, int C, int vocab, int64_t total4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total4) return;
+  const int c4 = (int)(i % (C / 4));
+  const int64_t tok = i / (C / 4);
+  const int t = (int)(tok % T);
+  int id = ids[tok];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const float4 w = __ldg(reinterpret_cast<const float4*>(word + (size_t)id * C) + c4);
+  const float4 pp = __ldg(reinterpret_cast<const float4*>(pos + (size_t)t * C) + c4);
+  const float4 ty = __ldg(reinterpret_cast<const float4*>(type0) + c4);
+  uint2 o;
+  o.x = pack_bf16x2(w.x + pp.x + ty.x, w.y + pp.y + ty.y);
+  o.y = pack_bf16x2(w.z + pp.z + ty.z, w.w + pp.w + ty.w);
+  *(reinterpret_cast<uint2*>(y + (size_t)tok * C) + c4) = o;
+}
+
+int embed_sum_dispatch(const int* ids, const float* word, const float* pos, const float* type0, void* y, int B, int T,
+                       int C, int vocab, cudaStream_t st) {
+  TOPO_CHECK(C % 4 == 0 && B > 0 && T > 0 && vocab > 0, TOPO_E_INVAL, "embed_sum: C must be a multiple of 4");
+  const int64_t total4 = (int64_t)B * T * (C / 4);
+  embed_sum_kernel<<<(unsigned)((total4 + 255) / 256), 256, 0, st>>>(ids, word, pos, type0, reinterpret_cast<bf16*>(y), T,
+                                                                   C, vocab, total4);
+  TOPO_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // ---- layout changes ------------------------------------------------------------------------------------
 // NCHW fp32 -> NHWC bf16 through a 32x32 smem transpose
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, bf16* __restrict__ y, int C, int HW, int y_ld) {

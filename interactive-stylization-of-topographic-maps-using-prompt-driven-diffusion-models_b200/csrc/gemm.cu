@@ -321,6 +321,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
       const bool plain = (rb == nullptr) && sg.act == TOPO_ACT_NONE;
       const bool silu = sg.act == TOPO_ACT_SILU;
+      const bool gelu = sg.act == TOPO_ACT_GELU;   // BERT intermediate (exact erf form, transformers "gelu")
+      const bool relu = sg.act == TOPO_ACT_RELU;   // text adapter MLP
       const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
       float* wstage = stage_f + (warp - 2) * (32 * 32);     // this warp's [32 rows][32 cols] fp32 staging
       float* srow = wstage + lane * 32;
@@ -384,6 +386,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               if (silu) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) x[j] = silu_f(x[j]);
+              } else if (gelu) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) x[j] = gelu_erf_f(x[j]);
+              } else if (relu) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) x[j] = fmaxf(x[j], 0.f);
               }
 #pragma unroll
               for (int j = 0; j < 4; ++j) v[4 * u + j] = x[j] * alpha;

@@ -12,7 +12,7 @@ from typing import Optional, Sequence, Tuple
 import torch
 
 from . import capi
-from .capi import ACT_GEGLU, ACT_NONE, ACT_SILU, TopoLinear, make_linear
+from .capi import ACT_GEGLU, ACT_GELU, ACT_NONE, ACT_RELU, ACT_SILU, TopoLinear, make_linear
 
 BF16 = torch.bfloat16
 
@@ -49,7 +49,7 @@ def prep_lora(A: torch.Tensor, B: torch.Tensor) -> Tuple[torch.Tensor, torch.Ten
 
 def head_pad(d: int) -> int:
     """Head dim padded to the next size the attention kernel is instantiated for."""
-    for dp in (48, 80, 160):
+    for dp in (48, 64, 80, 160):
         if d <= dp and (dp - d) < 16:
             return dp
     raise ValueError(f"head dim {d} unsupported (kernels are instantiated for 40->48, 80, 160)")
@@ -164,12 +164,21 @@ def conv3x3(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = Non
     return out
 
 
-def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp: int, scale: float) -> torch.Tensor:
-    """q [B,Nq,heads*dp], k/v [B,Nk,heads*dp] (bf16, padded head columns zero) -> o [B,Nq,heads*dp]."""
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp: int, scale: float,
+              kv_len: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q [B,Nq,heads*dp], k/v [B,Nk,heads*dp] (bf16, padded head columns zero) -> o [B,Nq,heads*dp].
+    ``kv_len`` (int32 [B] on the device): keys at or beyond the sample's length are masked (right-padded prompts)."""
     _cuda(q, "attention")
     Bn, Nq, ld = q.shape
     Nk = k.shape[1]
     o = torch.empty(Bn, Nq, heads * dp, dtype=BF16, device=q.device)
+    if kv_len is not None:
+        kv_len = kv_len.to(device=q.device, dtype=torch.int32).contiguous()
+        capi.check(capi.load_library().topo_attention_varlen(
+            capi.handle(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), Bn, heads, Nq, Nk, dp,
+            q.stride(1), k.stride(1), v.stride(1), o.stride(1), scale, kv_len.data_ptr(), capi.stream()),
+            "topo_attention_varlen")
+        return o
     capi.check(capi.load_library().topo_attention(
         capi.handle(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), Bn, heads, Nq, Nk, dp,
         q.stride(1), k.stride(1), v.stride(1), o.stride(1), scale, capi.stream()), "topo_attention")
@@ -252,6 +261,19 @@ def conv_direct(x: torch.Tensor, w_t: torch.Tensor, bias: Optional[torch.Tensor]
         Wd, Cin, Cout, ksize, stride, pad_lo, act, capi.ptr(add), 0 if add is None else add.shape[-1], int(out_fp32),
         capi.stream()), "topo_conv_direct")
     return out
+
+
+def embed_sum(ids: torch.Tensor, word: torch.Tensor, pos: torch.Tensor, type0: torch.Tensor) -> torch.Tensor:
+    """BERT embeddings ``word[ids] + pos[t] + type[0]`` -> bf16 [B, T, C] (fp32 tables, int ids on the device)."""
+    _cuda(ids, "embed_sum")
+    Bn, T = ids.shape
+    Cc = word.shape[1]
+    ids = ids.to(torch.int32).contiguous()
+    y = torch.empty(Bn, T, Cc, dtype=BF16, device=ids.device)
+    capi.check(capi.load_library().topo_embed_sum(capi.handle(), ids.data_ptr(), word.data_ptr(), pos.data_ptr(),
+                                                  type0.data_ptr(), y.data_ptr(), Bn, T, Cc, word.shape[0],
+                                                  capi.stream()), "topo_embed_sum")
+    return y
 
 
 def nchw_to_nhwc(x: torch.Tensor) -> torch.Tensor:

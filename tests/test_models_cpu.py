@@ -67,3 +67,21 @@ def test_no_cpu_forward():
     p = M.LoRACrossAttnProcessor(320, 768, key_states_skipped=True)
     with pytest.raises(AssertionError):
         p.skip_key_states(False)
+
+
+def test_text_encoder_containers():
+    from transformers import BertConfig, BertModel
+    from topo_b200.textenc import BERTTextEncoder, LastStateAdapter, build_text_encoder
+    assert list(LastStateAdapter(768, 768, 2).state_dict())[:4] == ["ff.0.weight", "ff.0.bias", "ff.2.weight", "ff.2.bias"]
+    assert "ff.15.weight" in LastStateAdapter(768, 768, 5).state_dict()          # addlrSD: 5 hidden layers, ff.15 = last Linear
+    bert = BertModel(BertConfig(num_hidden_layers=1, hidden_dropout_prob=0.1), add_pooling_layer=False)
+    te = build_text_encoder(hf_bert=bert, tokenizer=None, device="cpu")
+    assert te.hf_bert is bert and te.max_len == 77 and te.encode == te.encode_on_device
+    assert all(m.p == 0.0 for m in bert.modules() if isinstance(m, torch.nn.Dropout))   # disable_bert_dropout
+    assert not any(p.requires_grad for p in bert.parameters()) and all(p.requires_grad for p in te.adapter.parameters())
+    with pytest.raises(TopoError):
+        te.encode_ids(torch.zeros(1, 8, dtype=torch.long))      # CPU: no forward
+    with pytest.raises(TopoError):
+        te.encode(["a prompt"])                                   # no tokenizer
+    with pytest.raises(TopoError):
+        BERTTextEncoder(BertModel(BertConfig(num_hidden_layers=1, hidden_act="relu"), add_pooling_layer=False))

@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_models.py -m gpu -q -s -x > gpurun_out/models.log 2>&1; echo "models rc=$?"; grep -E "parity|Error|error|assert|passed|failed" gpurun_out/models.log | tail -40
+timeout 900 python -m pytest tests/test_gpu_textenc.py tests/test_gpu_attention.py tests/test_gpu_gemm.py -m gpu -q -s > gpurun_out/textenc.log 2>&1; echo "rc=$?"; grep -E "parity\] (BERT|encode|adapter)|Error|error|passed|failed" gpurun_out/textenc.log | tail -30
