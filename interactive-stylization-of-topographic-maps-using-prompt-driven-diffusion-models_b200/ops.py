@@ -192,7 +192,7 @@ def groupnorm_ws(B: int, G: int, device) -> torch.Tensor:
     n = capi.load_library().topo_groupnorm_ws_floats(B, G)
     key = (str(device), n)
     if key not in _gn_ws:
-        _gn_ws[key] = torch.empty(n, dtype=torch.float32, device=device)
+        _gn_ws[key] = torch.zeros(n, dtype=torch.float32, device=device)  # the fused kernel's counters start at zero
     return _gn_ws[key]
 
 

@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_textenc.py tests/test_gpu_attention.py tests/test_gpu_gemm.py -m gpu -q -s > gpurun_out/textenc.log 2>&1; echo "rc=$?"; grep -E "parity\] (BERT|encode|adapter)|Error|error|passed|failed" gpurun_out/textenc.log | tail -30
+timeout 600 python -m pytest tests/test_gpu_norm_elem.py -m gpu -q -x > gpurun_out/norm.log 2>&1; echo "norm rc=$?"; tail -3 gpurun_out/norm.log
+timeout 600 python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; echo "stage rc=$?"; grep -E "tiles=|groupnorm" gpurun_out/stage.log
