@@ -340,7 +340,25 @@ __device__ __forceinline__ float erf_as(float z) {
   const float e = 1.0f - pl * t * __expf(-a * a);
   return copysignf(e, z);
 }
-__device__ __forceinline__ float gelu_erf_f(float x) { return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float gelu_erf_as_f(float x) { return 0.5f * x * (1.0f + erf_as(x * 0.70710678118654752f)); }
+// Same function without the MUFU: Phi(x) = 0.5 + x R(x^2) with R a degree-8 least-squares/Chebyshev fit of
+// erf(x / sqrt 2) / (2x) on |x| <= 3 sqrt 2 and x clamped there (|Phi error| <= 1.3e-5, |gelu error| <= 7e-5 anywhere,
+// both far below the bf16 rounding of the product it feeds): 2 FMNMX + 1 FMUL + 9 FFMA + 1 FMUL = 13 issue slots
+// against ~28 and two MUFUs for the A&S form.  The GEGLU epilogue was issue bound on exactly this
+// (profiles/r01e_geglu.md: 41 instructions per output element, 61 % issue utilisation, tensor pipe 30 %).
+__device__ __forceinline__ float gelu_erf_f(float x) {
+  const float xc = fminf(fmaxf(x, -4.2426405f), 4.2426405f);
+  const float t = xc * xc;
+  float r = fmaf(5.623459337e-11f, t, -5.374264589e-09f);
+  r = fmaf(r, t, 2.270953274e-07f);
+  r = fmaf(r, t, -5.654654160e-06f);
+  r = fmaf(r, t, 9.372039494e-05f);
+  r = fmaf(r, t, -1.110463636e-03f);
+  r = fmaf(r, t, 9.822668508e-03f);
+  r = fmaf(r, t, -6.635588408e-02f);
+  r = fmaf(r, t, 3.989088237e-01f);
+  return x * fmaf(xc, r, 0.5f);
+}
 
 #endif  // __CUDACC__
 }  // namespace topo

@@ -51,6 +51,7 @@ struct alignas(64) GemmParams {
   int M, K;          // K = channels per tap
   int taps;          // 1 or 9
   int n_seg, m_tiles, total_tiles;
+  int nt_total;   // n tiles over all segments; > 0 selects the n-fastest tile order with contiguous per-CTA chunks
   // conv geometry
   int H, W, bw, bh, bb, tiles_w, tiles_h;
 };
@@ -80,17 +81,32 @@ struct TileCoord {
 template <int BN, bool CONV>
 __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
   TileCoord c;
-  int sgi = 0, rem = tile;
+  int sgi = 0, rem = tile, nt, mt;
+  if (p.nt_total > 0) {
+    // n fastest: the tiles that share an x (A) tile are consecutive, every CTA walks a contiguous chunk of the list,
+    // so x is streamed from HBM exactly once (the W tiles are small and stay in L2)
+    mt = tile / p.nt_total;
+    nt = tile - mt * p.nt_total;
 #pragma unroll
-  for (int i = 0; i < MAX_SEG - 1; ++i) {
-    const int cnt = p.seg[i].n_tiles * p.m_tiles;
-    if (sgi == i && i + 1 < p.n_seg && rem >= cnt) {
-      rem -= cnt;
-      sgi = i + 1;
+    for (int i = 0; i < MAX_SEG - 1; ++i) {
+      if (sgi == i && i + 1 < p.n_seg && nt >= p.seg[i].n_tiles) {
+        nt -= p.seg[i].n_tiles;
+        sgi = i + 1;
+      }
     }
+  } else {
+#pragma unroll
+    for (int i = 0; i < MAX_SEG - 1; ++i) {
+      const int cnt = p.seg[i].n_tiles * p.m_tiles;
+      if (sgi == i && i + 1 < p.n_seg && rem >= cnt) {
+        rem -= cnt;
+        sgi = i + 1;
+      }
+    }
+    nt = rem / p.m_tiles;
+    mt = rem - nt * p.m_tiles;
   }
   c.seg = sgi;
-  const int nt = rem / p.m_tiles, mt = rem - nt * p.m_tiles;
   c.n0 = nt * BN;
   c.cw0 = c.ch0 = c.cb0 = 0;
   if (CONV) {
@@ -130,6 +146,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lb_full + 4);
 
   const int warp = threadIdx.x >> 5;
+  // tile walk: strided (m-fastest order) or a contiguous chunk per CTA (n-fastest order)
+  const int chunk = (p.total_tiles + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int tile_begin = p.nt_total > 0 ? (int)blockIdx.x * chunk : (int)blockIdx.x;
+  const int tile_end = p.nt_total > 0 ? min(p.total_tiles, tile_begin + chunk) : p.total_tiles;
+  const int tile_step = p.nt_total > 0 ? 1 : (int)gridDim.x;
   const int lane = threadIdx.x & 31;
   const int kc = p.K / BK;
   const int num_kb = p.taps * kc;
@@ -171,7 +192,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const TileCoord c = tile_coord<BN, CONV>(p, tile);
         const GemmSegDev& sg = p.seg[c.seg];
         if (RPAD) {
@@ -209,7 +230,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const int buf = it & 1;
         const uint32_t tmem_acc = tmem_base + buf * BN;
         const uint32_t tmem_t = tmem_base + T_COL;
@@ -261,7 +282,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     int it = 0;
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const TileCoord c = tile_coord<BN, CONV>(p, tile);
       const GemmSegDev& sg = p.seg[c.seg];
       const int buf = it & 1;
@@ -497,7 +518,18 @@ static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   }
   (void)grid;
   const int ctas = p.total_tiles < sms ? p.total_tiles : sms;  // persistent: one CTA per SM walks the tile list
-  kfn<<<ctas, GEMM_THREADS, L::TOTAL, st>>>(p);
+  static int order = -1;  // TOPO_TILE_ORDER=m restores the m-fastest walk (tuning / A-B runs)
+  if (order < 0) {
+    const char* e = getenv("TOPO_TILE_ORDER");
+    order = (e && e[0] == 'm') ? 0 : 1;
+  }
+  GemmParams q = p;
+  q.nt_total = 0;
+  if (order == 1 && p.total_tiles > ctas) {
+    for (int i = 0; i < p.n_seg; ++i) q.nt_total += p.seg[i].n_tiles;
+    if (q.nt_total < 2) q.nt_total = 0;  // a single n tile: both orders coincide, keep the strided walk
+  }
+  kfn<<<ctas, GEMM_THREADS, L::TOTAL, st>>>(q);
   TOPO_CUDA(cudaGetLastError());
   return 0;
 }

@@ -253,6 +253,70 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const bf16* __restrict__
   }
 }
 
+// C = G * V * 8: G lanes share a row (V 16-byte vectors each, every lane fully used), 32 / G rows per warp, so a
+// warp has 32 * V independent 16-byte loads in flight (C = 320: four rows per warp instead of one row on 40 of 64 lane
+// slots).  Same exact two-pass variance, reductions over the G-lane group only.
+template <int G, int V>
+__global__ void __launch_bounds__(256) layernorm_group_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+                                                             int y_ld, int M, const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps) {
+  constexpr int C = G * V * 8;
+  constexpr int RPW = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int l = lane % G;
+  const int row = (blockIdx.x * 8 + (threadIdx.x >> 5)) * RPW + lane / G;
+  const bool ok = row < M;
+  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)(ok ? row : 0) * x_ld);
+  float f[V][8];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    unpack8(__ldg(xr + l + k * G), f[k]);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += f[k][i];
+  }
+#pragma unroll
+  for (int o = G / 2; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s * (1.0f / C);
+  float q = 0.f;
+#pragma unroll
+  for (int k = 0; k < V; ++k)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float d = f[k][i] - mean;
+      q = fmaf(d, d, q);
+    }
+#pragma unroll
+  for (int o = G / 2; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+  const float rstd = rsqrtf(q * (1.0f / C) + eps);
+  if (!ok) return;
+  uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * y_ld);
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const int v = l + k * G;
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v);
+    const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v + 1);
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v);
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v + 1);
+    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = fmaf((f[k][i] - mean) * rstd, gg[i], bb[i]);
+    uint4 o;
+    o.x = pack_bf16x2(r[0], r[1]); o.y = pack_bf16x2(r[2], r[3]);
+    o.z = pack_bf16x2(r[4], r[5]); o.w = pack_bf16x2(r[6], r[7]);
+    yr[v] = o;
+  }
+}
+
+template <int G, int V>
+static void launch_ln_group(const bf16* x, int x_ld, bf16* y, int y_ld, int M, const float* gamma, const float* beta,
+                            float eps, cudaStream_t st) {
+  const int rows_per_block = 8 * (32 / G);
+  layernorm_group_kernel<G, V><<<(M + rows_per_block - 1) / rows_per_block, 256, 0, st>>>(x, x_ld, y, y_ld, M, gamma, beta, eps);
+}
+
 int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int M, int C,
                        float eps, cudaStream_t st) {
   TOPO_CHECK(C % 8 == 0 && C <= 2048, TOPO_E_INVAL, "layernorm: C=%d unsupported (multiple of 8, <= 2048)", C);
@@ -260,7 +324,15 @@ int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
   const int grid = (M + 7) / 8;
   const bf16* xx = reinterpret_cast<const bf16*>(x);
   bf16* yy = reinterpret_cast<bf16*>(y);
-  if (C <= 512)
+  if (C == 320)
+    launch_ln_group<8, 5>(xx, x_ld, yy, y_ld, M, gamma, beta, eps, st);
+  else if (C == 640)
+    launch_ln_group<16, 5>(xx, x_ld, yy, y_ld, M, gamma, beta, eps, st);
+  else if (C == 1280)
+    launch_ln_group<32, 5>(xx, x_ld, yy, y_ld, M, gamma, beta, eps, st);
+  else if (C == 768)
+    launch_ln_group<32, 3>(xx, x_ld, yy, y_ld, M, gamma, beta, eps, st);
+  else if (C <= 512)
     layernorm_kernel<2><<<grid, 256, 0, st>>>(xx, x_ld, yy, y_ld, M, C, gamma, beta, eps);
   else if (C <= 1280)
     layernorm_kernel<5><<<grid, 256, 0, st>>>(xx, x_ld, yy, y_ld, M, C, gamma, beta, eps);

@@ -23,7 +23,7 @@ def test_groupnorm_silu(B, HW, C, silu, eps):
     assert_close(y, ref, 8e-3, f"groupnorm B{B} HW{HW} C{C} silu={silu}")
 
 
-@pytest.mark.parametrize("M,C", [(8192, 320), (2048, 640), (77, 1280), (513, 2048)])
+@pytest.mark.parametrize("M,C", [(8192, 320), (2048, 640), (77, 1280), (513, 2048), (8190, 320), (1001, 640), (77, 1280), (231, 768)])
 def test_layernorm(M, C):
     from topo_b200 import ops
     x = (rnd(M, C, seed=1) * 2 + 0.5).to(BF16)

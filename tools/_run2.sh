@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
-for np in 0 2; do
-TOPO_ATTN_NPOLY=$np ITERS=1 timeout 600 ncu --set full --import-source on --clock-control none -k regex:attention_kernel -s 2 -c 1 -f -o gpurun_out/attn_np$np python tools/gemm_bench.py Nk4096 > gpurun_out/ncu_attn_np$np.log 2>&1; echo "ncu np=$np rc=$?"
-done
-ls -la gpurun_out/
+timeout 600 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x 2>&1 | tail -2
+echo "== n-fastest"; ITERS=5 python tools/gemm_bench.py 2>&1 | grep -E "gemm|conv" 
+echo "== m-fastest"; TOPO_TILE_ORDER=m ITERS=5 python tools/gemm_bench.py 2>&1 | grep -E "gemm|conv"
