@@ -141,6 +141,9 @@ int topo_upsample2x(topo_handle_t h, const void* x, int x_ld, void* y, int y_ld,
                     void* stream);
 /* im2col for the three stride-2 Downsample convs: y [B*Ho*Wo, 9*C] (tap-major) */
 int topo_im2col3x3_s2(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream);
+/* im2col for the narrow 3x3/s1/p1 input convs (9*C <= 64: the 4-channel latent conv_in of the UNet, the ControlNet and
+ * the VAE decoder): y [B*H*W, 64] bf16, column = tap*C + c, zero beyond 9*C; consumed by topo_lora_linear with K = 64 */
+int topo_im2col3x3_s1_k64(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream);
 int topo_add_bf16(topo_handle_t h, const void* a, int a_ld, const void* b, int b_ld, void* y, int y_ld, int M, int C,
                   void* stream);
 /* decoded tile [-1,1] NHWC (fp32 or bf16) -> uint8 HWC: x*127.5+127.5, clip, truncate (BaseModel/evaluateCN.py:101-103) */

@@ -93,6 +93,7 @@ int nchw_to_nhwc_dispatch(const float* x, void* y, int B, int C, int HW, int y_l
 int nhwc_to_nchw_dispatch(const void* x, int x_is_f32, int x_ld, float* y, int B, int C, int HW, cudaStream_t st);
 int upsample2x_dispatch(const void* x, int x_ld, void* y, int y_ld, int B, int H, int W, int C, cudaStream_t st);
 int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st);
+int im2col_s1_k64_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st);
 int add_dispatch(const void* a, int a_ld, const void* b, int b_ld, void* y, int y_ld, int M, int C, cudaStream_t st);
 int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, cudaStream_t st);
 int softmax_rows_dispatch(const void* x, int x_ld, void* y, int y_ld, int M, int N, float scale, cudaStream_t st);
@@ -276,6 +277,12 @@ int topo_upsample2x(topo_handle_t h, const void* x, int x_ld, void* y, int y_ld,
                     void* stream) {
   H_CHECK(h);
   return upsample2x_dispatch(x, x_ld, y, y_ld, B, H, W, C, ST(stream));
+}
+
+int topo_im2col3x3_s1_k64(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream) {
+  H_CHECK(h);
+  TOPO_CHECK(x && y, TOPO_E_INVAL, "topo_im2col3x3_s1_k64: null argument");
+  return im2col_s1_k64_dispatch(x, x_ld, y, B, H, W, C, ST(stream));
 }
 
 int topo_im2col3x3_s2(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream) {

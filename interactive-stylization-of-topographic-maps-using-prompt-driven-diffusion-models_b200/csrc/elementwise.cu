@@ -255,6 +255,39 @@ __global__ void im2col_s2_kernel(const bf16* __restrict__ x, int x_ld, bf16* __r
     *(reinterpret_cast<uint4*>(y + ((size_t)pix * 9 + tap) * C) + v) = u;
   }
 }
+// ---- im2col for the narrow 3x3 stride-1 pad-1 input convs (latent conv_in: C = 4): y [B*H*W, 64], column = tap*C + c,
+//      columns >= 9*C zero.  One thread per 16-byte output chunk; turns a 36-deep direct convolution (8 TFLOP/s on the
+//      CUDA cores) into a one-K-block tensor-core GEMM.
+__global__ void __launch_bounds__(256) im2col_s1_k64_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y, int B, int H,
+                                                           int W, int C, int64_t total) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int chunk = (int)(idx & 7);
+  const int64_t pix = idx >> 3;
+  const int w = (int)(pix % W);
+  const int h = (int)((pix / W) % H);
+  const int b = (int)(pix / ((int64_t)W * H));
+  __align__(16) bf16 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int e = chunk * 8 + i;
+    const int tap = e / C, c = e - tap * C;
+    const int hi = h + tap / 3 - 1, wi = w + tap % 3 - 1;
+    const bool ok = tap < 9 && hi >= 0 && hi < H && wi >= 0 && wi < W;
+    v[i] = ok ? x[((size_t)(b * H + hi) * W + wi) * x_ld + c] : __float2bfloat16(0.f);
+  }
+  *reinterpret_cast<uint4*>(y + pix * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
+}
+
+int im2col_s1_k64_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st) {
+  TOPO_CHECK(C >= 1 && 9 * C <= 64, TOPO_E_INVAL, "im2col3x3_s1_k64: 9*C must fit one 64-wide K block (C = %d)", C);
+  const int64_t total = (int64_t)B * H * W * 8;
+  im2col_s1_k64_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(reinterpret_cast<const bf16*>(x), x_ld,
+                                                                       reinterpret_cast<bf16*>(y), B, H, W, C, total);
+  TOPO_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st) {
   TOPO_CHECK(C % 8 == 0 && x_ld % 8 == 0 && H % 2 == 0 && W % 2 == 0, TOPO_E_INVAL, "im2col3x3_s2: bad shape");
   const int64_t total = (int64_t)B * (H / 2) * (W / 2) * 9 * (C / 8);

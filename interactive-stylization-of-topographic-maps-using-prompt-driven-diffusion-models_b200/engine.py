@@ -285,6 +285,12 @@ class PConvIn:
         self.w = ops.conv_direct_weight(conv.weight.detach().to(device))
         self.b = _dev(conv.bias, device, torch.float32)
         self.cin, self.cout, self.k, self.stride = conv.in_channels, conv.out_channels, conv.kernel_size[0], conv.stride[0]
+        # narrow 3x3/s1 input convs (4-channel latents): im2col into ONE 64-wide K block + tensor-core GEMM
+        self.gemm = None
+        if self.k == 3 and self.stride == 1 and 9 * self.cin <= 64:
+            w = torch.zeros(self.cout, 64, device=device)
+            w[:, :9 * self.cin] = conv.weight.detach().to(device).float().permute(0, 2, 3, 1).reshape(self.cout, -1)
+            self.gemm = Lin(w.to(BF16).contiguous(), self.b)
 
 
 def _pack_layer(m, device):
@@ -413,6 +419,11 @@ def run_convin(c: PConvIn, x4: torch.Tensor, act: int = ACT_NONE, add: Optional[
                out_fp32: bool = False) -> torch.Tensor:
     _count()
     Bn, H, W, _ = x4.shape
+    if c.gemm is not None and act == ACT_NONE:
+        cols = ops.im2col3x3_s1_k64(x4)
+        _count()
+        res = None if add is None else add.reshape(Bn * H * W, -1)
+        return gemm(cols, c.gemm, res=res, out_fp32=out_fp32).view(Bn, H, W, -1)
     Ho, Wo = H // c.stride, W // c.stride
     return _rec("conv_direct", 2.0 * Bn * Ho * Wo * c.cout * c.k * c.k * c.cin,
                 2.0 * (x4.numel() + Bn * Ho * Wo * c.cout * (2 if out_fp32 else 1)),

@@ -304,6 +304,17 @@ def upsample2x(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def im2col3x3_s1_k64(x: torch.Tensor) -> torch.Tensor:
+    """NHWC bf16 [B,H,W,C] with 9*C <= 64 -> [B*H*W, 64] (tap-major columns, zero padded): the narrow input convs as
+    one-K-block GEMMs."""
+    _cuda(x, "im2col3x3_s1_k64")
+    Bn, H, Wd, Cc = x.shape
+    y = torch.empty(Bn * H * Wd, 64, dtype=BF16, device=x.device)
+    capi.check(capi.load_library().topo_im2col3x3_s1_k64(capi.handle(), x.data_ptr(), x.stride(2), y.data_ptr(), Bn, H, Wd,
+                                                         Cc, capi.stream()), "topo_im2col3x3_s1_k64")
+    return y
+
+
 def im2col3x3_s2(x: torch.Tensor) -> torch.Tensor:
     Bn, H, Wd, Cc = x.shape
     y = torch.empty(Bn * (H // 2) * (Wd // 2), 9 * Cc, dtype=BF16, device=x.device)

@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_norm_elem.py -m gpu -q -x > gpurun_out/norm.log 2>&1; echo "norm rc=$?"; tail -3 gpurun_out/norm.log
-timeout 600 python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; echo "stage rc=$?"; grep -E "tiles=|groupnorm" gpurun_out/stage.log
+python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; echo "stage rc=$?"; grep -E "tiles=|conv_direct" gpurun_out/stage.log
+timeout 900 python -m pytest tests/test_gpu_e2e.py -m gpu -x -q > gpurun_out/e2e.log 2>&1; echo "e2e rc=$?"; tail -3 gpurun_out/e2e.log
