@@ -56,10 +56,13 @@ struct alignas(64) GemmParams {
   int H, W, bw, bh, bb, tiles_w, tiles_h;
 };
 
-template <int BN, int RPAD, int STAGES>
+// PAIR: two CTAs of a cluster run one M = 256 UMMA (cta_group::2); each holds its own 128 x rows and HALF of the W tile
+// (BN / 2 rows), so a stage is 32 KB instead of 48 KB at BN = 256: six stages instead of four, and a third less L2 -> SM
+// traffic per FLOP.
+template <int BN, int RPAD, int STAGES, bool PAIR = false>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int W_BYTES = BN * BK * 2;
+  static constexpr int W_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int LA_BYTES = RPAD * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + W_BYTES + LA_BYTES;
   static constexpr int LB_BYTES = BN * RPAD * 2;
@@ -125,9 +128,10 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
   return c;
 }
 
-template <int BN, int RPAD, int STAGES, bool CONV>
+template <int BN, int RPAD, int STAGES, bool CONV, bool PAIR = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
-  using L = GemmSmem<BN, RPAD, STAGES>;
+  static_assert(!PAIR || RPAD == 0, "the CTA-pair variant has no LoRA side product");
+  using L = GemmSmem<BN, RPAD, STAGES, PAIR>;
   // no static shared memory in this kernel: the dynamic window starts at the CTA's 1 KB-aligned base (SWIZZLE_128B
   // needs it; a violation becomes a launch failure), which saves the 1 KB of slack the fourth BN = 256 stage needs
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -149,10 +153,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   // tile walk: strided (m-fastest order) or a contiguous chunk per CTA (n-fastest order)
-  const int chunk = (p.total_tiles + (int)gridDim.x - 1) / (int)gridDim.x;
-  const int tile_begin = p.nt_total > 0 ? (int)blockIdx.x * chunk : (int)blockIdx.x;
-  const int tile_end = p.nt_total > 0 ? min(p.total_tiles, tile_begin + chunk) : p.total_tiles;
-  const int tile_step = p.nt_total > 0 ? 1 : (int)gridDim.x;
+  // PAIR: the cluster walks a contiguous chunk of PAIR tiles (two adjacent m tiles x one n tile, n fastest); CTA `rank`
+  // owns m tile 2 * pair + rank (an odd tail pairs the last m tile with an out-of-range one: zero-filled loads, masked stores)
+  const int rank = PAIR ? (int)cluster_ctarank() : 0;
+  const int walkers = PAIR ? (int)gridDim.x / 2 : (int)gridDim.x;
+  const int walker = PAIR ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int walk_total = PAIR ? ((p.m_tiles + 1) / 2) * p.nt_total : p.total_tiles;
+  const int chunk = (walk_total + walkers - 1) / walkers;
+  const int tile_begin = p.nt_total > 0 ? walker * chunk : walker;
+  const int tile_end = p.nt_total > 0 ? min(walk_total, tile_begin + chunk) : walk_total;
+  const int tile_step = p.nt_total > 0 ? 1 : walkers;
+  auto tile_id = [&](int t) { return PAIR ? (2 * (t / p.nt_total) + rank) * p.nt_total + t % p.nt_total : t; };
   const int lane = threadIdx.x & 31;
   const int kc = p.K / BK;
   const int num_kb = p.taps * kc;
@@ -174,7 +185,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], EPI_THREADS);
+      mbar_init(&tempty[i], PAIR ? 2 * EPI_THREADS : EPI_THREADS);  // PAIR: the peer's epilogue arrives on the leader's barrier
     }
     mbar_init(lb_full, 1);
     mbar_init(lb_empty, 1);
@@ -182,9 +193,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     mbar_init(t_ready, 128);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  if (warp == 1) {
+    if (PAIR) tmem_alloc2(tmem_slot, TMEM_COLS);
+    else tmem_alloc(tmem_slot, TMEM_COLS);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // the peer's barriers must be initialised before anything is signalled across
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -195,7 +210,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       uint32_t phase = 0;
       int it = 0;
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
-        const TileCoord c = tile_coord<BN, CONV>(p, tile);
+        const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
         const GemmSegDev& sg = p.seg[c.seg];
         if (RPAD) {
           mbar_wait(lb_empty, (it & 1) ^ 1);  // previous tile's LoRA-up MMA is done with lb_tile
@@ -207,6 +222,27 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           uint8_t* a_s = smem + stage * L::STAGE_BYTES;
           uint8_t* w_s = a_s + L::A_BYTES;
           uint8_t* la_s = w_s + L::W_BYTES;
+          if (PAIR) {
+            // both CTAs' bytes are credited to the LEADER's full barrier (the only one the MMA issuer waits on)
+            if (rank == 0) mbar_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
+            const uint32_t fb = leader_bar(&full[stage]);
+            const int n_left = sg.N - c.n0;
+            const int n_eff = n_left >= BN ? BN : ((n_left + 31) & ~31);
+            if (CONV) {
+              const int tap = kb / kc;
+              const int c0 = (kb - tap * kc) * BK;
+              const int dy = tap / 3 - 1, dx = tap % 3 - 1;
+              tma2_load_4d(a_s, &p.tm_x, fb, c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
+            } else {
+              tma2_load_2d(a_s, &p.tm_x, fb, kb * BK, c.m0);
+            }
+            tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * (n_eff / 2));  // this CTA's half of the W rows
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+            continue;
+          }
           mbar_expect_tx(&full[stage], L::STAGE_BYTES);
           if (CONV) {
             const int tap = kb / kc;
@@ -226,8 +262,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (PAIR: the leader CTA issues for both) =====================
+    if (lane == 0 && rank == 0) {
       constexpr uint32_t idesc_side = make_idesc_bf16(BM, RPAD ? RPAD : 16);
       int stage = 0;
       uint32_t phase = 0;
@@ -237,10 +273,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         const uint32_t tmem_acc = tmem_base + buf * BN;
         const uint32_t tmem_t = tmem_base + T_COL;
         // the last N tile of a segment only multiplies the columns that exist (UMMA N is a run-time field, multiple of 16)
-        const TileCoord c = tile_coord<BN, CONV>(p, tile);
+        const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
         const int n_left = p.seg[c.seg].N - c.n0;
-        const uint32_t n_eff = n_left >= BN ? BN : ((n_left + 15) & ~15);
-        const uint32_t idesc_main = make_idesc_bf16(BM, n_eff);
+        const uint32_t n_eff = n_left >= BN ? BN : (PAIR ? ((n_left + 31) & ~31) : ((n_left + 15) & ~15));
+        const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, n_eff);
         mbar_wait(&tempty[buf], ((it >> 1) & 1) ^ 1);  // epilogue drained this accumulator (two tiles ago)
         tc_fence_after();
         for (int kb = 0; kb < num_kb; ++kb) {
@@ -252,10 +288,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
-            umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
+            if (PAIR) umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
+            else umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
             if (RPAD) umma_bf16(tmem_t, ad, kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
           }
-          umma_commit(&empty[stage]);
+          if (PAIR) umma2_commit(&empty[stage]);   // frees the stage in BOTH CTAs
+          else umma_commit(&empty[stage]);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -273,7 +311,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, 1);
           umma_commit(lb_empty);
         }
-        umma_commit(&tfull[buf]);
+        if (PAIR) umma2_commit(&tfull[buf]);
+        else umma_commit(&tfull[buf]);
       }
     }
   } else {
@@ -281,11 +320,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     const int q = warp & 3;
     const int hsel = (warp - 2) >> 2;
     const int et = threadIdx.x - 64;
+    auto tempty_arrive = [&](int b) {   // PAIR: both CTAs' accumulators belong to the leader's MMA issuer
+      if (PAIR && rank != 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[b]), 0));
+      else mbar_arrive(&tempty[b]);
+    };
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     int it = 0;
     for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
-      const TileCoord c = tile_coord<BN, CONV>(p, tile);
+      const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
       const GemmSegDev& sg = p.seg[c.seg];
       const int buf = it & 1;
       const uint32_t tmem_acc = tmem_base + buf * BN;
@@ -358,7 +401,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         if (out_n0 + c32 * 32 >= out_N) {        // chunk entirely beyond the segment's last column (N tail)
           if (ch == nchunk - 1) {
             tc_fence_before();
-            mbar_arrive(&tempty[buf]);
+            tempty_arrive(buf);
           }
           continue;
         }
@@ -423,7 +466,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         }
         if (ch == nchunk - 1) {
           tc_fence_before();
-          mbar_arrive(&tempty[buf]);             // accumulator drained: the MMA warp may start tile it+2 into it
+          tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+2 into it
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u)
@@ -492,16 +535,63 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (PAIR) cluster_sync_all();   // neither CTA may exit (or free TMEM) while the other can still signal / read it
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) tmem_dealloc2(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+static int sm_count();
+
+// CTA-pair launch: clusters of two CTAs, one cluster per TPC.
+template <int BN, int STAGES, bool CONV>
+static int launch_gemm_pair(const GemmParams& p, cudaStream_t st) {
+  using L = GemmSmem<BN, 0, STAGES, true>;
+  auto kfn = gemm_kernel<BN, 0, STAGES, CONV, true>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    attr_set = true;
+  }
+  GemmParams q = p;
+  q.nt_total = 0;
+  for (int i = 0; i < p.n_seg; ++i) q.nt_total += p.seg[i].n_tiles;
+  const int pair_tiles = ((p.m_tiles + 1) / 2) * q.nt_total;
+  int clusters = sm_count() / 2;
+  if (clusters > pair_tiles) clusters = pair_tiles;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * clusters);
+  cfg.blockDim = dim3(GEMM_THREADS);
+  cfg.dynamicSmemBytes = L::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  TOPO_CUDA(cudaLaunchKernelEx(&cfg, kfn, q));
+  return 0;
+}
+
+// TOPO_PAIR=0 disables the CTA-pair kernels (A/B runs)
+static bool pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TOPO_PAIR");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 template <int BN, int RPAD, int STAGES, bool CONV>
 static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
@@ -564,13 +654,13 @@ static int pick_bn(int m_tiles, int N, int r_pad, int n_seg, int act) {
   return tiles256 >= 2 * sm_count() ? 256 : 128;
 }
 
-static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int BN) {
+static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int BN, int box_n = 0) {
   TOPO_CHECK(s.W && s.out, TOPO_E_INVAL, "topo_linear_t: W/out must be non-null");
   TOPO_CHECK(s.r_pad == 0 || s.r_pad == 16 || s.r_pad == 32, TOPO_E_INVAL, "r_pad must be 0, 16 or 32 (got %d)", s.r_pad);
   TOPO_CHECK(s.act != TOPO_ACT_GEGLU || (s.N % BN == 0), TOPO_E_INVAL, "GEGLU needs N %% %d == 0", BN);
   uint64_t dims[2] = {(uint64_t)taps * K, (uint64_t)s.N};
   uint64_t strides[1] = {(uint64_t)taps * K * 2};
-  uint32_t box[2] = {BK, (uint32_t)BN};
+  uint32_t box[2] = {BK, (uint32_t)(box_n ? box_n : BN)};  // box_n = BN / 2: each CTA of a pair loads half of the W rows
   int rc = make_tmap(&d.tm_w, s.W, 2, dims, strides, box, 128);
   if (rc) return rc;
   if (s.r_pad) {
@@ -619,9 +709,14 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   int rc = make_tmap(&p.tm_x, x, 2, dims, strides, box, 128);
   if (rc) return rc;
   int r_pad = segs[0].r_pad, maxN = 0;
+  // CTA pairs (cta_group::2, six 32 KB stages) for the long-K, pipeline-latency-bound problems with at least one pair
+  // tile per cluster; short-K projections are epilogue bound and lose from coupling two epilogues to one issuer
+  // (measured: K = 1280 / 2560 -> +5 / +9 %, K = 320 GEGLU -> -16 %)
+  const bool pair = BN == 256 && r_pad == 0 && K >= 1024 && pair_enabled() &&
+                    ((M + 2 * BM - 1) / (2 * BM)) >= sm_count() / 2;
   for (int i = 0; i < n_seg; ++i) {
     TOPO_CHECK(segs[i].r_pad == r_pad, TOPO_E_INVAL, "all segments of one call must share r_pad");
-    rc = fill_seg(p.seg[i], segs[i], K, 1, BN);
+    rc = fill_seg(p.seg[i], segs[i], K, 1, BN, pair ? BN / 2 : 0);
     if (rc) return rc;
     maxN = segs[i].N > maxN ? segs[i].N : maxN;
   }
@@ -633,6 +728,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   p.total_tiles = 0;
   for (int i = 0; i < n_seg; ++i) p.total_tiles += p.seg[i].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
+  if (pair) return launch_gemm_pair<256, 6, false>(p, st);
   // BN = 256: a fourth stage (192 KB in flight) pays when the K loop is long (latency bound: 3 -> 4 stages took the
   // 3x3 convs from 930 to 1010-1380 TFLOP/s); short-K projections are epilogue bound and keep 3 stages
   if (BN == 256) return K >= 1024 ? launch_gemm<256, 0, 4, false>(p, grid, st) : launch_gemm<256, 0, 3, false>(p, grid, st);
@@ -661,7 +757,8 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   uint32_t box[4] = {BK, (uint32_t)bw, (uint32_t)bh, (uint32_t)bb};
   int rc = make_tmap(&p.tm_x, x, 4, dims, strides, box, 128);
   if (rc) return rc;
-  rc = fill_seg(p.seg[0], *seg, C, 9, BN);
+  const bool pair = BN == 256 && pair_enabled() && (B * H * W) / (2 * BM) >= sm_count() / 2;
+  rc = fill_seg(p.seg[0], *seg, C, 9, BN, pair ? BN / 2 : 0);
   if (rc) return rc;
   p.M = B * H * W;
   p.K = C;
@@ -678,6 +775,7 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   p.m_tiles = p.tiles_w * p.tiles_h * tiles_b;
   p.total_tiles = p.seg[0].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
+  if (pair) return launch_gemm_pair<256, 6, true>(p, st);
   if (BN == 256) return launch_gemm<256, 0, 4, true>(p, grid, st);
   return launch_gemm<128, 0, 6, true>(p, grid, st);
 }
