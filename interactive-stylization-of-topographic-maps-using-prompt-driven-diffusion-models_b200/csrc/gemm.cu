@@ -742,7 +742,13 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   TOPO_CHECK(x_ld % 8 == 0, TOPO_E_INVAL, "conv3x3: x_ld must be a multiple of 8");
   TOPO_CHECK(seg->r_pad == 0, TOPO_E_INVAL, "conv3x3: LoRA not supported on convolutions");
   TOPO_CHECK(seg->act != TOPO_ACT_GEGLU, TOPO_E_INVAL, "conv3x3: GEGLU epilogue not supported on convolutions");
-  const int BN = pick_bn((B * H * W + BM - 1) / BM, seg->N, 0, 1, seg->act);
+  int BN = pick_bn((B * H * W + BM - 1) / BM, seg->N, 0, 1, seg->act);
+  // CTA pairs (256 x 256 pair tiles, six stages) whenever they give at least ~half a wave of work: the long K loop of
+  // a 3x3 conv (9 * C / 64 k-blocks) is pipeline-latency bound, which the deeper pair pipeline relieves even at the
+  // 8x8 / 16x16 levels where the tile count is small (measured 580 -> see profiles/r01e_gemm.md)
+  const int pair_tiles = ((B * H * W + 2 * BM - 1) / (2 * BM)) * ((seg->N + 255) / 256);
+  const bool pair = pair_enabled() && seg->N >= 192 && pair_tiles >= 40;
+  if (pair) BN = 256;
   GemmParams p;
   memset(&p, 0, sizeof(p));
   const int bw = W < BM ? W : BM;
@@ -757,7 +763,6 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   uint32_t box[4] = {BK, (uint32_t)bw, (uint32_t)bh, (uint32_t)bb};
   int rc = make_tmap(&p.tm_x, x, 4, dims, strides, box, 128);
   if (rc) return rc;
-  const bool pair = BN == 256 && pair_enabled() && (B * H * W) / (2 * BM) >= sm_count() / 2;
   rc = fill_seg(p.seg[0], *seg, C, 9, BN, pair ? BN / 2 : 0);
   if (rc) return rc;
   p.M = B * H * W;
