@@ -141,6 +141,10 @@ int topo_upsample2x(topo_handle_t h, const void* x, int x_ld, void* y, int y_ld,
                     void* stream);
 /* im2col for the three stride-2 Downsample convs: y [B*Ho*Wo, 9*C] (tap-major) */
 int topo_im2col3x3_s2(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream);
+/* same with pad_lo zero rows/columns before the image (1 = the call above; 0 = ldm's VAE-encoder Downsample, which pads
+ * (0,1,0,1) and convolves with padding 0 — upstream ldm/modules/diffusionmodules/model.py Downsample.forward) */
+int topo_im2col3x3_s2_pad(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, int pad_lo,
+                          void* stream);
 /* im2col for the narrow 3x3/s1/p1 input convs (9*C <= 64: the 4-channel latent conv_in of the UNet, the ControlNet and
  * the VAE decoder): y [B*H*W, 64] bf16, column = tap*C + c, zero beyond 9*C; consumed by topo_lora_linear with K = 64 */
 int topo_im2col3x3_s1_k64(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream);

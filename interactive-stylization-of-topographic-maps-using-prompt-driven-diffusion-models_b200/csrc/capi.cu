@@ -92,7 +92,7 @@ int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bi
 int nchw_to_nhwc_dispatch(const float* x, void* y, int B, int C, int HW, int y_ld, cudaStream_t st);
 int nhwc_to_nchw_dispatch(const void* x, int x_is_f32, int x_ld, float* y, int B, int C, int HW, cudaStream_t st);
 int upsample2x_dispatch(const void* x, int x_ld, void* y, int y_ld, int B, int H, int W, int C, cudaStream_t st);
-int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st);
+int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, int pad, cudaStream_t st);
 int im2col_s1_k64_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st);
 int add_dispatch(const void* a, int a_ld, const void* b, int b_ld, void* y, int y_ld, int M, int C, cudaStream_t st);
 int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, cudaStream_t st);
@@ -287,7 +287,13 @@ int topo_im2col3x3_s1_k64(topo_handle_t h, const void* x, int x_ld, void* y, int
 
 int topo_im2col3x3_s2(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, void* stream) {
   H_CHECK(h);
-  return im2col_s2_dispatch(x, x_ld, y, B, H, W, C, ST(stream));
+  return im2col_s2_dispatch(x, x_ld, y, B, H, W, C, 1, ST(stream));
+}
+
+int topo_im2col3x3_s2_pad(topo_handle_t h, const void* x, int x_ld, void* y, int B, int H, int W, int C, int pad_lo,
+                          void* stream) {
+  H_CHECK(h);
+  return im2col_s2_dispatch(x, x_ld, y, B, H, W, C, pad_lo, ST(stream));
 }
 
 int topo_add_bf16(topo_handle_t h, const void* a, int a_ld, const void* b, int b_ld, void* y, int y_ld, int M, int C,

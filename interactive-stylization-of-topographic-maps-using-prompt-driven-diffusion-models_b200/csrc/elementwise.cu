@@ -235,8 +235,9 @@ int upsample2x_dispatch(const void* x, int x_ld, void* y, int y_ld, int B, int H
   return 0;
 }
 
-// ---- im2col for 3x3 stride-2 pad-1 (Downsample.op): y [B*Ho*Wo, 9*C], column = tap*C + c --------------
-__global__ void im2col_s2_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y, int B, int H, int W, int C) {
+// ---- im2col for 3x3 stride-2 (Downsample.op: pad 1 both sides; VAE encoder Downsample: pad = 0, one zero row/column
+//      AFTER the image): y [B*Ho*Wo, 9*C], column = tap*C + c ------------------------------------------
+__global__ void im2col_s2_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y, int B, int H, int W, int C, int pad) {
   const int Ho = H / 2, Wo = W / 2;
   const int vpr = C >> 3;
   const int64_t total = (int64_t)B * Ho * Wo * 9 * vpr;
@@ -248,7 +249,7 @@ __global__ void im2col_s2_kernel(const bf16* __restrict__ x, int x_ld, bf16* __r
     const int wo = (int)(pix % Wo);
     const int ho = (int)((pix / Wo) % Ho);
     const int b = (int)(pix / ((int64_t)Wo * Ho));
-    const int hi = ho * 2 + tap / 3 - 1, wi = wo * 2 + tap % 3 - 1;
+    const int hi = ho * 2 + tap / 3 - pad, wi = wo * 2 + tap % 3 - pad;
     uint4 u = make_uint4(0, 0, 0, 0);
     if (hi >= 0 && hi < H && wi >= 0 && wi < W)
       u = __ldg(reinterpret_cast<const uint4*>(x + ((size_t)(b * H + hi) * W + wi) * x_ld) + v);
@@ -288,12 +289,13 @@ int im2col_s1_k64_dispatch(const void* x, int x_ld, void* y, int B, int H, int W
   return 0;
 }
 
-int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st) {
+int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, int pad, cudaStream_t st) {
+  TOPO_CHECK(pad == 0 || pad == 1, TOPO_E_INVAL, "im2col3x3_s2: pad_lo must be 0 or 1");
   TOPO_CHECK(C % 8 == 0 && x_ld % 8 == 0 && H % 2 == 0 && W % 2 == 0, TOPO_E_INVAL, "im2col3x3_s2: bad shape");
   const int64_t total = (int64_t)B * (H / 2) * (W / 2) * 9 * (C / 8);
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  im2col_s2_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), B, H, W, C);
+  im2col_s2_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), B, H, W, C, pad);
   TOPO_CUDA(cudaGetLastError());
   return 0;
 }

@@ -616,6 +616,12 @@ class TopoEngine:
         return self.vae.decode(z)
 
     @torch.no_grad()
+    def encode_moments(self, x: torch.Tensor) -> torch.Tensor:
+        """Posterior moments of ``first_stage_model.encode`` (``vis_metrics.py:86``)."""
+        if self.vae is None or not hasattr(self.vae, "e_conv_in"):
+            raise capi.TopoError("encode_first_stage: model was built without the VAE encoder")
+        return self.vae.encode_moments(x)
+
     def decode_to_u8(self, z: torch.Tensor) -> torch.Tensor:
         """decode_first_stage + uint8 HWC conversion on the device → [B, 8H, 8W, 3] uint8."""
         if self.vae is None:
@@ -696,6 +702,59 @@ class PVae:
                 b[:co.out_channels] = co.bias.detach().to(device).float()
             self.conv_out_tc = Lin(ops.conv3x3_weight(w), b)
             self.out_ch = co.out_channels
+        if hasattr(vae, "encoder"):
+            self._pack_encoder(vae, device)
+
+    def _pack_encoder(self, vae, device):
+        enc = vae.encoder
+        self.e_conv_in = PConvIn(enc.conv_in, device)
+        self.e_levels = []
+        for lvl in enc.down:
+            blocks = [PVRes(b, device) for b in lvl.block]
+            down = pack_conv3x3(lvl.downsample.conv, device) if hasattr(lvl, "downsample") else None
+            self.e_levels.append((blocks, down))
+        self.e_mid1, self.e_attn, self.e_mid2 = (PVRes(enc.mid.block_1, device), PVAttn(enc.mid.attn_1, device),
+                                                 PVRes(enc.mid.block_2, device))
+        self.e_norm_out = pack_norm(enc.norm_out, device)
+        # conv_out (512 -> 2z) then quant_conv (1x1, 2z -> 2z) composed into ONE 3x3 conv: Wq (Wc * x + bc) + bq,
+        # output channels zero-padded to the smallest UMMA N (16)
+        co, qc = enc.conv_out, vae.quant_conv
+        Wq = qc.weight.detach().to(device).float().view(qc.out_channels, qc.in_channels)
+        w = torch.einsum("om,mikl->oikl", Wq, co.weight.detach().to(device).float())
+        b = Wq @ co.bias.detach().to(device).float() + qc.bias.detach().to(device).float()
+        self.mom_ch = qc.out_channels
+        if self.mom_ch > 16 or co.in_channels % 64 != 0:
+            raise capi.TopoError("VAE encoder: conv_out wider than 16 moments or Cin not a multiple of 64 is not implemented")
+        wp = torch.zeros(16, co.in_channels, 3, 3, device=device)
+        wp[:self.mom_ch] = w
+        bp = torch.zeros(16, device=device)
+        bp[:self.mom_ch] = b
+        self.e_conv_out = Lin(ops.conv3x3_weight(wp), bp)
+
+    def encode_moments(self, x: torch.Tensor) -> torch.Tensor:
+        """``quant_conv(encoder(x))`` -> fp32 NCHW ``[B, 2z, H/8, W/8]`` (mean | logvar), x ``[B,3,H,W]`` fp32."""
+        B, _, H, W = x.shape
+        if H % 8 or W % 8:
+            raise capi.TopoError("VAE encode: H and W must be multiples of 8")
+        h = run_convin(self.e_conv_in, ops.nchw_to_nhwc(x.float()))
+        _count()
+        h = h.view(B * H * W, -1)
+        for blocks, down in self.e_levels:
+            for rb in blocks:
+                h = rb.run(h, B, H, W)
+            if down is not None:   # pad (0,1,0,1) + stride-2 conv: im2col with no leading padding, then a GEMM
+                cols = ops.im2col3x3_s2(h.view(B, H, W, -1), pad_lo=0)
+                _count()
+                H, W = H // 2, W // 2
+                h = gemm(cols, down)
+        h = self.e_mid1.run(h, B, H, W)
+        h = self.e_attn.run(h, B, H, W)
+        h = self.e_mid2.run(h, B, H, W)
+        h = gn(h, B, self.e_norm_out, True)
+        if W % 8 != 0:
+            raise capi.TopoError("VAE encode: latent width must be a multiple of 8 for the tensor-core conv_out")
+        m = conv3(h, B, H, W, self.e_conv_out, out_fp32=True).view(B, H, W, 16)[..., :self.mom_ch]
+        return ops.nhwc_to_nchw(m)
 
     def decode(self, z: torch.Tensor, u8: bool = False) -> torch.Tensor:
         B, _, H, W = z.shape

@@ -397,14 +397,75 @@ class Decoder(_NoForward):
         self.conv_out = nn.Conv2d(block_in, 3, 3, padding=1)
 
 
+class _VaeDownsample(_NoForward):
+    """ldm ``Downsample(with_conv=True)``: zero-pad (0,1,0,1) then ``Conv2d(c, c, 3, stride=2, padding=0)``."""
+
+    def __init__(self, c):
+        super().__init__()
+        self.conv = nn.Conv2d(c, c, 3, stride=2, padding=0)
+
+
+class _DownLevel(_NoForward):
+    pass
+
+
+class Encoder(_NoForward):
+    """ldm ``Encoder(ch=128, ch_mult=(1,2,4,4), num_res_blocks=2, attn_resolutions=[], double_z=True)`` — upstream
+    ``ldm/modules/diffusionmodules/model.py``; state-dict keys ``down.{i}.block.{j}.*``, ``down.{i}.downsample.conv.*``,
+    ``mid.*``, ``norm_out``, ``conv_out``.  Called through ``encode_first_stage`` (``vis_metrics.py:86``)."""
+
+    def __init__(self, cfg: ModelConfig):
+        super().__init__()
+        ch, mult = cfg.vae_ch, tuple(cfg.vae_ch_mult)
+        self.conv_in = nn.Conv2d(3, ch, 3, padding=1)
+        self.down = nn.ModuleList()
+        block_in = ch
+        for i_level in range(len(mult)):
+            lvl = _DownLevel()
+            lvl.block = nn.ModuleList()
+            block_out = ch * mult[i_level]
+            for _ in range(cfg.vae_num_res_blocks):
+                lvl.block.append(ResnetBlock(block_in, block_out))
+                block_in = block_out
+            if i_level != len(mult) - 1:
+                lvl.downsample = _VaeDownsample(block_in)
+            self.down.append(lvl)
+        self.mid = _Mid(block_in)
+        self.norm_out = _vgn(block_in)
+        self.conv_out = nn.Conv2d(block_in, 2 * cfg.vae_z_channels, 3, padding=1)
+
+
+class DiagonalGaussianDistribution:
+    """ldm ``DiagonalGaussianDistribution`` (upstream ``ldm/modules/distributions/distributions.py``): ``parameters`` =
+    ``[B, 2z, h, w]`` moments; logvar clamped to [-30, 20]; ``sample() = mean + std * randn``; ``mode() = mean``."""
+
+    def __init__(self, parameters: torch.Tensor, deterministic: bool = False):
+        self.parameters = parameters
+        self.mean, self.logvar = torch.chunk(parameters, 2, dim=1)
+        self.logvar = torch.clamp(self.logvar, -30.0, 20.0)
+        self.deterministic = deterministic
+        self.std = torch.exp(0.5 * self.logvar)
+        self.var = torch.exp(self.logvar)
+        if deterministic:
+            self.var = self.std = torch.zeros_like(self.mean)
+
+    def sample(self):
+        return self.mean + self.std * torch.randn(self.mean.shape, device=self.parameters.device)
+
+    def mode(self):
+        return self.mean
+
+
 class AutoencoderKL(_NoForward):
-    """Decoder half only (the path never encodes during sampling; ``encode_first_stage`` is used
-    by training / ``validate_step`` only and is out of scope)."""
+    """``encode`` (Encoder + ``quant_conv`` -> posterior; ``validate_step`` / training targets) and ``decode``
+    (``post_quant_conv`` + Decoder; every sampled tile).  Both halves run on the kernels (``engine.PVae``)."""
 
     def __init__(self, cfg: ModelConfig):
         super().__init__()
         self.decoder = Decoder(cfg)
         self.post_quant_conv = nn.Conv2d(cfg.vae_z_channels, cfg.vae_z_channels, 1)
+        self.encoder = Encoder(cfg)
+        self.quant_conv = nn.Conv2d(2 * cfg.vae_z_channels, 2 * cfg.vae_z_channels, 1)
 
 
 class DiffusionWrapper(nn.Module):
@@ -473,6 +534,21 @@ class ControlLDM(nn.Module):
     @torch.no_grad()
     def decode_first_stage(self, z):
         return self.engine().decode_first_stage(z)
+
+    @torch.no_grad()
+    def encode_first_stage(self, x):
+        """``first_stage_model.encode(x)`` -> posterior (``vis_metrics.py:86``); x ``[B,3,H,W]`` in [-1,1]."""
+        return DiagonalGaussianDistribution(self.engine().encode_moments(x))
+
+    def get_first_stage_encoding(self, encoder_posterior):
+        """ldm ``LatentDiffusion.get_first_stage_encoding``: ``scale_factor * posterior.sample()`` (a tensor passes through)."""
+        if isinstance(encoder_posterior, DiagonalGaussianDistribution):
+            z = encoder_posterior.sample()
+        elif isinstance(encoder_posterior, torch.Tensor):
+            z = encoder_posterior
+        else:
+            raise NotImplementedError(f"encoder_posterior of type '{type(encoder_posterior)}' not yet implemented")
+        return self.scale_factor * z
 
     def q_sample(self, x_start, t, noise=None):
         noise = torch.randn_like(x_start) if noise is None else noise

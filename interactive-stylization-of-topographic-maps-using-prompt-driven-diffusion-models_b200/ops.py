@@ -315,11 +315,13 @@ def im2col3x3_s1_k64(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
-def im2col3x3_s2(x: torch.Tensor) -> torch.Tensor:
+def im2col3x3_s2(x: torch.Tensor, pad_lo: int = 1) -> torch.Tensor:
+    """NHWC bf16 -> [B*(H/2)*(W/2), 9*C] for a 3x3 stride-2 conv.  ``pad_lo=1``: symmetric padding 1 (UNet Downsample);
+    ``pad_lo=0``: the VAE encoder's pad-(0,1,0,1) form."""
     Bn, H, Wd, Cc = x.shape
     y = torch.empty(Bn * (H // 2) * (Wd // 2), 9 * Cc, dtype=BF16, device=x.device)
-    capi.check(capi.load_library().topo_im2col3x3_s2(capi.handle(), x.data_ptr(), Cc, y.data_ptr(), Bn, H, Wd, Cc,
-                                                     capi.stream()), "topo_im2col3x3_s2")
+    capi.check(capi.load_library().topo_im2col3x3_s2_pad(capi.handle(), x.data_ptr(), Cc, y.data_ptr(), Bn, H, Wd, Cc,
+                                                         pad_lo, capi.stream()), "topo_im2col3x3_s2_pad")
     return y
 
 

@@ -166,12 +166,14 @@ def sample_preview(model, textenc, batch, device, steps=30, scale=7.5, eta=0.0, 
 
 @torch.no_grad()
 def validate_step(model, textenc, batch, device, max_length=77, iters=64, fixed_t=None, fixed_noise=None, z=None):
-    """ε-MSE over ``iters`` random timesteps (``vis_metrics.py:73-116``).  The reference VAE-encodes ``batch['gt']``;
-    the encoder half of the VAE is off the sampling path, so a latent ``z`` (or ``batch['z']``) must be supplied."""
+    """ε-MSE over ``iters`` random timesteps (``vis_metrics.py:73-116``): ``z = get_first_stage_encoding(
+    encode_first_stage(gt))`` (VAE encoder on the kernels), then per iteration ``q_sample`` → ``apply_model`` → mse.
+    ``z`` (or ``batch['z']``) may be supplied to skip the encoder (pre-encoded validation sets)."""
     seg = batch["seg"].to(device=device, dtype=torch.float32)
     z = z if z is not None else batch.get("z")
     if z is None:
-        raise capi.TopoError("validate_step: supply the VAE latent `z` (encode_first_stage is outside the hot path)")
+        gt = batch["gt"].to(device=device, dtype=torch.float32)
+        z = model.get_first_stage_encoding(model.encode_first_stage(gt))
     z = z.to(device=device, dtype=torch.float32)
     B = z.size(0)
     c_cross = textenc.encode(batch["prompt"]).to(device=device, dtype=torch.float32)

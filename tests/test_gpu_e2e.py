@@ -144,3 +144,44 @@ def test_ctrlora_30step_batch_and_u8_tiles():
     diff = (u8.int() - ref_u8.int()).abs()
     print(f"[parity] ctrlora 30-step tiles: cos={cos:.6f} mean|du8|={diff.float().mean().item():.2f} max={int(diff.max())}")
     assert cos >= 0.999
+
+
+def test_vae_encode_and_validate_step():
+    """encode_first_stage (VAE encoder + quant_conv on the kernels) vs the oracle's ldm Encoder, then validate_step
+    (vis_metrics.py:73-116) with fixed t / noise against the oracle's ε-MSE."""
+    from oracle import ldm_oracle as O
+    from topo_b200 import sampling
+    model = synth.build_model("ctrlora").cuda()
+    sd = {k: v.float() for k, v in model.state_dict().items()}
+    scales = synth.lora_scales(model)
+    B = 2
+    gt = (synth.make_hint(B, 256, seed=5) * 2 - 1).cuda()
+    seg, ctx = synth.make_hint(B, 256).cuda(), synth.make_ctx(B).cuda()
+    with torch.no_grad():
+        post = model.encode_first_stage(gt)
+        ref = O.encode_first_stage(sd, gt)
+    mom = post.parameters
+    err = (mom - ref).abs().max().item() / ref.abs().max().item()
+    cos = _cos(mom, ref)
+    print(f"[parity] VAE encode moments {tuple(mom.shape)}: rel_max={err:.3e} cos={cos:.6f}")
+    assert mom.shape == ref.shape == (B, 8, 32, 32) and mom.dtype == torch.float32
+    assert cos >= 0.9995 and err <= 3e-2
+    assert torch.equal(post.mode(), mom[:, :4]) and post.sample().shape == (B, 4, 32, 32)
+    z_ref = O.get_first_stage_encoding(ref)                          # mode, scaled
+    assert torch.allclose(model.get_first_stage_encoding(post.mode()), model.scale_factor * mom[:, :4])
+
+    class TE:
+        def encode(self, prompts):
+            return ctx
+
+    t = torch.tensor([700, 120], device="cuda")
+    noise = synth.make_xT(B, 32, seed=9).cuda()
+    with torch.no_grad():
+        ours = sampling.validate_step(model, TE(), {"seg": seg, "prompt": ["a", "b"]}, "cuda", iters=2, fixed_t=t,
+                                      fixed_noise=noise, z=z_ref)
+        want = O.validate_step(sd, z_ref, ctx, seg, [t, t], [noise, noise], scales=scales)
+        full = sampling.validate_step(model, TE(), {"seg": seg, "gt": gt, "prompt": ["a", "b"]}, "cuda", iters=1,
+                                      fixed_t=t, fixed_noise=noise)
+    print(f"[parity] validate_step eps-MSE: ours={ours:.6f} oracle={want:.6f} (with encoder+sampled posterior: {full:.6f})")
+    assert abs(ours - want) <= 2e-2 * abs(want)
+    assert full == full and full > 0

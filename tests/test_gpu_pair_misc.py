@@ -103,3 +103,17 @@ def test_conv_direct_pad_after_only():
     ref = F.conv2d(F.pad(x.float().permute(0, 3, 1, 2), (0, 1, 0, 1)), w.float(), b, stride=2).permute(0, 2, 3, 1)
     assert y.shape == ref.shape
     assert_close(y, ref, TOL, "conv_direct pad_lo=0 stride 2")
+
+
+def test_im2col_s2_pad_after_gemm_is_vae_downsample():
+    """ldm VAE-encoder Downsample: F.pad(x, (0,1,0,1)) + Conv2d(C, C, 3, stride=2, padding=0) as im2col(pad_lo=0) + GEMM."""
+    ops = _ops()
+    B, H, C, N = 2, 64, 128, 128
+    x = rnd(B, H, H, C, seed=1).to(BF16)
+    w, b = rnd(N, C, 3, 3, seed=2, scale=(9 * C) ** -0.5).to(BF16), rnd(N, seed=3)
+    y = ops.linear(ops.im2col3x3_s2(x, pad_lo=0), ops.conv3x3_weight(w), b).view(B, H // 2, H // 2, N)
+    ref = F.conv2d(F.pad(x.float().permute(0, 3, 1, 2), (0, 1, 0, 1)), w.float(), b, stride=2).permute(0, 2, 3, 1)
+    assert_close(y, ref, TOL, "im2col_s2 pad_lo=0 + gemm")
+    y1 = ops.linear(ops.im2col3x3_s2(x), ops.conv3x3_weight(w), b).view(B, H // 2, H // 2, N)
+    ref1 = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), b, stride=2, padding=1).permute(0, 2, 3, 1)
+    assert_close(y1, ref1, TOL, "im2col_s2 pad_lo=1 + gemm")
