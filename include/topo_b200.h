@@ -153,9 +153,21 @@ int topo_add_bf16(topo_handle_t h, const void* a, int a_ld, const void* b, int b
 /* decoded tile [-1,1] NHWC (fp32 or bf16) -> uint8 HWC: x*127.5+127.5, clip, truncate (BaseModel/evaluateCN.py:101-103) */
 int topo_tile_to_u8(topo_handle_t h, const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C,
                     void* stream);
+/* same layout, the metrics script's conversion: ((x+1)*127.5).clamp(0,255).round() (half to even)
+ * (LoRA_modified/quantitative_metrics.py:206-207) */
+int topo_tile_to_u8_round(topo_handle_t h, const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C,
+                          void* stream);
 /* row softmax for the single VAE mid attention (materialised scores): y = softmax(x * scale) */
 int topo_softmax_rows(topo_handle_t h, const void* x, int x_ld, void* y, int y_ld, int M, int N, float scale,
                       void* stream);
+/* Tile metrics (LoRA_modified/quantitative_metrics.py:164-195: mse_rgb, psnr_rgb, color_histogram_l1_255) as one device
+ * pass over T tile pairs.  pred / gt hold integral values 0..255, as uint8 (is_f32 = 0) or float32 (is_f32 = 1), laid
+ * out [T, n_pixels, 3] (planar = 0, HWC: the output of topo_tile_to_u8) or [T, 3, n_pixels] (planar = 1, the
+ * reference's CHW tensors).  lut[256] maps a value to its histogram bin (host-built, numpy.histogram semantics).
+ * ACCUMULATES: sse[t] += sum (pred - gt)^2 over the tile (exact, uint64); hist[t][0][c][b] / hist[t][1][c][b] += the
+ * number of pred / gt values of channel c in bin b (uint32), bins <= 64.  Zero both before the first call. */
+int topo_tile_metrics(topo_handle_t h, const void* pred, const void* gt, int is_f32, int planar, int T, int64_t n_pixels,
+                      const uint8_t* lut, int bins, uint64_t* sse, uint32_t* hist, void* stream);
 
 #ifdef __cplusplus
 }

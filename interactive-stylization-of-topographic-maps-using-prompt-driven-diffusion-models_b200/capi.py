@@ -22,8 +22,8 @@ SYMBOLS = [
     "topo_create", "topo_destroy", "topo_last_error", "topo_version", "topo_lora_linear", "topo_conv3x3",
     "topo_attention", "topo_attention_varlen", "topo_embed_sum", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
     "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_conv_direct",
-    "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_im2col3x3_s1_k64",
-    "topo_add_bf16", "topo_tile_to_u8", "topo_softmax_rows", "topo_geglu_tile",
+    "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_tile_metrics", "topo_im2col3x3_s1_k64",
+    "topo_add_bf16", "topo_tile_to_u8", "topo_tile_to_u8_round", "topo_softmax_rows", "topo_geglu_tile",
 ]
 
 
@@ -80,10 +80,12 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_nhwc_to_nchw_f32.argtypes = [vp, vp, i32, i32, vp, i32, i32, i32, vp]
     lib.topo_upsample2x.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]
     lib.topo_im2col3x3_s2.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, vp]
+    lib.topo_tile_metrics.argtypes = [vp, vp, vp, i32, i32, i32, i64, vp, i32, vp, vp, vp]
     lib.topo_im2col3x3_s2_pad.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]
     lib.topo_im2col3x3_s1_k64.argtypes = [vp, vp, i32, vp, i32, i32, i32, i32, vp]
     lib.topo_add_bf16.argtypes = [vp, vp, i32, vp, i32, vp, i32, i32, i32, vp]
     lib.topo_tile_to_u8.argtypes = [vp, vp, i32, i32, vp, i64, i32, vp]
+    lib.topo_tile_to_u8_round.argtypes = [vp, vp, i32, i32, vp, i64, i32, vp]
     lib.topo_softmax_rows.argtypes = [vp, vp, i32, vp, i32, i32, i32, f32, vp]
     _lib = lib
     return lib

@@ -92,10 +92,12 @@ int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bi
 int nchw_to_nhwc_dispatch(const float* x, void* y, int B, int C, int HW, int y_ld, cudaStream_t st);
 int nhwc_to_nchw_dispatch(const void* x, int x_is_f32, int x_ld, float* y, int B, int C, int HW, cudaStream_t st);
 int upsample2x_dispatch(const void* x, int x_ld, void* y, int y_ld, int B, int H, int W, int C, cudaStream_t st);
+int tile_metrics_dispatch(const void* pred, const void* gt, int is_f32, int planar, int T, int64_t n_pixels,
+                          const uint8_t* lut, int bins, unsigned long long* sse, uint32_t* hist, cudaStream_t st);
 int im2col_s2_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, int pad, cudaStream_t st);
 int im2col_s1_k64_dispatch(const void* x, int x_ld, void* y, int B, int H, int W, int C, cudaStream_t st);
 int add_dispatch(const void* a, int a_ld, const void* b, int b_ld, void* y, int y_ld, int M, int C, cudaStream_t st);
-int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, cudaStream_t st);
+int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, int mode, cudaStream_t st);
 int softmax_rows_dispatch(const void* x, int x_ld, void* y, int y_ld, int M, int N, float scale, cudaStream_t st);
 
 }  // namespace topo
@@ -305,13 +307,26 @@ int topo_add_bf16(topo_handle_t h, const void* a, int a_ld, const void* b, int b
 int topo_tile_to_u8(topo_handle_t h, const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C,
                     void* stream) {
   H_CHECK(h);
-  return tile_to_u8_dispatch(x, x_is_f32, x_ld, y, n_pixels, C, ST(stream));
+  return tile_to_u8_dispatch(x, x_is_f32, x_ld, y, n_pixels, C, 0, ST(stream));
+}
+
+int topo_tile_to_u8_round(topo_handle_t h, const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C,
+                          void* stream) {
+  H_CHECK(h);
+  return tile_to_u8_dispatch(x, x_is_f32, x_ld, y, n_pixels, C, 1, ST(stream));
 }
 
 int topo_softmax_rows(topo_handle_t h, const void* x, int x_ld, void* y, int y_ld, int M, int N, float scale,
                       void* stream) {
   H_CHECK(h);
   return softmax_rows_dispatch(x, x_ld, y, y_ld, M, N, scale, ST(stream));
+}
+
+int topo_tile_metrics(topo_handle_t h, const void* pred, const void* gt, int is_f32, int planar, int T, int64_t n_pixels,
+                      const uint8_t* lut, int bins, uint64_t* sse, uint32_t* hist, void* stream) {
+  H_CHECK(h);
+  return tile_metrics_dispatch(pred, gt, is_f32, planar, T, n_pixels, lut, bins,
+                               reinterpret_cast<unsigned long long*>(sse), hist, ST(stream));
 }
 
 }  // extern "C"

@@ -330,25 +330,29 @@ int add_dispatch(const void* a, int a_ld, const void* b, int b_ld, void* y, int 
 }
 
 // ---- decoded tile -> uint8 HWC ------------------------------------------------------------------------
+// mode 0: x*127.5+127.5, clip, truncate (BaseModel/evaluateCN.py:101-103, numpy .astype(uint8));
+// mode 1: ((x+1)*127.5).clamp(0,255).round() (LoRA_modified/quantitative_metrics.py:206-207; torch.round = half to even)
 template <typename T>
-__global__ void tile_to_u8_kernel(const T* __restrict__ x, int x_ld, uint8_t* __restrict__ y, int64_t n_pixels, int C) {
+__global__ void tile_to_u8_kernel(const T* __restrict__ x, int x_ld, uint8_t* __restrict__ y, int64_t n_pixels, int C, int mode) {
   const int64_t total = n_pixels * C;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t pix = idx / C;
     const int c = (int)(idx % C);
-    float v = (float)x[pix * x_ld + c] * 127.5f + 127.5f;
+    const float xv = (float)x[pix * x_ld + c];
+    float v = mode ? __fmul_rn(__fadd_rn(xv, 1.f), 127.5f) : __fadd_rn(__fmul_rn(xv, 127.5f), 127.5f);
     v = fminf(fmaxf(v, 0.f), 255.f);
-    y[idx] = (uint8_t)v;  // truncation, as numpy .astype(uint8) after clip
+    y[idx] = (uint8_t)(mode ? rintf(v) : v);
   }
 }
-int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, cudaStream_t st) {
+int tile_to_u8_dispatch(const void* x, int x_is_f32, int x_ld, uint8_t* y, int64_t n_pixels, int C, int mode, cudaStream_t st) {
+  TOPO_CHECK(mode == 0 || mode == 1, TOPO_E_INVAL, "tile_to_u8: mode must be 0 (truncate) or 1 (round)");
   const int64_t total = n_pixels * C;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (x_is_f32)
-    tile_to_u8_kernel<float><<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(x), x_ld, y, n_pixels, C);
+    tile_to_u8_kernel<float><<<blocks, 256, 0, st>>>(reinterpret_cast<const float*>(x), x_ld, y, n_pixels, C, mode);
   else
-    tile_to_u8_kernel<bf16><<<blocks, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), x_ld, y, n_pixels, C);
+    tile_to_u8_kernel<bf16><<<blocks, 256, 0, st>>>(reinterpret_cast<const bf16*>(x), x_ld, y, n_pixels, C, mode);
   TOPO_CUDA(cudaGetLastError());
   return 0;
 }

@@ -333,14 +333,37 @@ def add(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     return y
 
 
-def tile_to_u8(x: torch.Tensor) -> torch.Tensor:
-    """NHWC [-1,1] (bf16 or fp32) -> uint8 NHWC (BaseModel/evaluateCN.py:101-103)."""
+def tile_to_u8(x: torch.Tensor, round_half_even: bool = False) -> torch.Tensor:
+    """NHWC [-1,1] (bf16 or fp32) -> uint8 NHWC.  Default: ``x*127.5+127.5``, clip, truncate
+    (BaseModel/evaluateCN.py:101-103); ``round_half_even``: ``((x+1)*127.5).clamp(0,255).round()``
+    (LoRA_modified/quantitative_metrics.py:206-207)."""
+    _cuda(x, "tile_to_u8")
     Cc = x.shape[-1]
     ld = x.stride(-2)  # a channel slice of a wider pixel-major buffer is fine (pixels must be evenly strided)
     y = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
-    capi.check(capi.load_library().topo_tile_to_u8(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), ld,
-                                                   y.data_ptr(), x.numel() // Cc, Cc, capi.stream()), "topo_tile_to_u8")
+    lib = capi.load_library()
+    fn = lib.topo_tile_to_u8_round if round_half_even else lib.topo_tile_to_u8
+    capi.check(fn(capi.handle(), x.data_ptr(), int(x.dtype == torch.float32), ld, y.data_ptr(), x.numel() // Cc, Cc,
+                  capi.stream()), "topo_tile_to_u8")
     return y
+
+
+def tile_metrics(pred: torch.Tensor, gt: torch.Tensor, lut: torch.Tensor, bins: int, planar: bool):
+    """One pass over T tile pairs holding integral 0..255 values (uint8 or fp32; ``[T,P,3]`` or planar ``[T,3,P]``):
+    returns ``(sse int64 [T], hist int32 [T,2,3,bins])`` — exact counts."""
+    _cuda(pred, "tile_metrics")
+    if pred.shape != gt.shape or pred.dtype != gt.dtype or pred.dtype not in (torch.uint8, torch.float32):
+        raise capi.TopoError(f"tile_metrics: pred/gt must be same-shape uint8 or float32 tensors, got {pred.shape} "
+                             f"{pred.dtype} / {gt.shape} {gt.dtype}")
+    pred, gt = pred.contiguous(), gt.contiguous()
+    T = pred.shape[0]
+    n_pixels = pred[0].numel() // 3 if T else 1
+    sse = torch.zeros(T, dtype=torch.int64, device=pred.device)
+    hist = torch.zeros(T, 2, 3, bins, dtype=torch.int32, device=pred.device)
+    capi.check(capi.load_library().topo_tile_metrics(
+        capi.handle(), pred.data_ptr(), gt.data_ptr(), int(pred.dtype == torch.float32), int(planar), T, n_pixels,
+        lut.data_ptr(), bins, sse.data_ptr(), hist.data_ptr(), capi.stream()), "topo_tile_metrics")
+    return sse, hist
 
 
 def softmax_rows(x: torch.Tensor, scale: float) -> torch.Tensor:

@@ -1,2 +1,3 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_e2e.py::test_vae_encode_and_validate_step tests/test_gpu_pair_misc.py::test_im2col_s2_pad_after_gemm_is_vae_downsample -x -q -s > gpurun_out/enc.log 2>&1; echo "rc=$?"; grep -E "parity|passed|failed|Error|error" gpurun_out/enc.log | head -20
+timeout 600 python -m pytest tests/test_metrics.py -x -q -s -m gpu > gpurun_out/metrics.log 2>&1; echo "rc=$?"; grep -E "parity|passed|failed|Error|error|assert" gpurun_out/metrics.log | head -20
+timeout 900 python -m pytest tests/test_gpu_e2e.py tests/test_gpu_norm_elem.py -x -q -m gpu 2>&1 | tail -3
