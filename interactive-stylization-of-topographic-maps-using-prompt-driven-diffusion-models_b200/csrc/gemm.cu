@@ -333,14 +333,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const int buf = it & 1;
       const uint32_t tmem_acc = tmem_base + buf * BN;
       float* sbias = sbias_all + buf * BN;
-      // bias tile -> smem (double-buffered by tile parity; the barrier also orders tile i-1's staging reads
-      // before tile i's staging writes across the two warps that share a row quadrant? no: each warp only touches
-      // its own rows x columns of the staging tile, so __syncwarp suffices for staging; the barrier is for sbias)
-      if (et < BN) {
-        const int n = c.n0 + et;
-        sbias[et] = (sg.bias && n < sg.N) ? __ldg(sg.bias + n) : 0.f;
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(EPI_THREADS) : "memory");
+      // (the bias tile is written per warp after the accumulator wait, see below: no CTA-wide epilogue barrier)
 
       if (RPAD && hsel == 0) {
         // s*T (fp32, TMEM) -> bf16 K-major swizzled smem tile, the A operand of the LoRA-up UMMA
@@ -368,9 +361,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         mbar_arrive(t_ready);
       }
 
-      mbar_wait(&tfull[buf], (it >> 1) & 1);
-      tc_fence_after();
-
       // ---- the warp owns rows [q*32, +32) x output columns [hsel*colsw, +colsw) of the tile and walks them in
       //      32-column chunks: phase A (row per thread: TMEM -> registers -> bias/activation -> fp32 staging, 4 KB per
       //      warp, 16-byte units XOR-swizzled with row&7) then phase B (8 lanes per row, 4 rows per instruction, all 8
@@ -382,7 +372,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const int NC = geglu ? BN / 2 : BN;        // output columns this tile produces
       const int out_n0 = geglu ? c.n0 / 2 : c.n0;
       const int out_N = geglu ? sg.N / 2 : sg.N;
-      const int nchunk = NC / 64;                // 32-column chunks per warp
+      // the tile's valid 32-column output chunks are dealt out ALTERNATELY to the two warps that share a TMEM lane
+      // quadrant (c32 = hsel, hsel + 2, ...), so a narrow N-tail tile still keeps all eight warps busy
+      int valid_cols = out_N - out_n0;
+      valid_cols = valid_cols < 0 ? 0 : (valid_cols > NC ? NC : valid_cols);
+      const int n_my = (((valid_cols + 31) >> 5) - hsel + 1) >> 1;
       const float alpha = sg.alpha;
       const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
       const bool plain = (rb == nullptr) && sg.act == TOPO_ACT_NONE;
@@ -395,22 +389,61 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const int sub = lane >> 3;                 // phase B: row within a 4-row group
       const int unit = lane & 7;                 // phase B: 16-byte unit (4 columns) within the 32-column chunk
       const int rows_left = p.M - (c.m0 + q * 32 + sub);
-#pragma unroll 1
-      for (int ch = 0; ch < nchunk; ++ch) {
-        const int c32 = hsel * nchunk + ch;      // 32-column chunk index among the tile's OUTPUT columns
-        if (out_n0 + c32 * 32 >= out_N) {        // chunk entirely beyond the segment's last column (N tail)
-          if (ch == nchunk - 1) {
-            tc_fence_before();
-            tempty_arrive(buf);
-          }
-          continue;
+      // residual rows are prefetched ONE CHUNK AHEAD (the first chunk before the accumulator is even complete): the
+      // short-K projections were bound by the serial TMEM-load -> staging -> LDG -> STG latency chain of each chunk
+      const bool res_vec = vec_ok && sg.res != nullptr;
+      const bf16* res_row0 = res_vec ? sg.res + (size_t)(c.m0 + q * 32 + sub) * sg.res_ld + sg.res_col : nullptr;
+      const size_t res_step4 = (size_t)4 * sg.res_ld;
+      auto load_res = [&](int chn, uint2 (&dst)[8]) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dst[k] = make_uint2(0u, 0u);
+        const int nn = out_n0 + (hsel + 2 * chn) * 32 + unit * 4;
+        if (res_vec && chn < n_my && nn < out_N) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (k * 4 < rows_left) dst[k] = __ldg(reinterpret_cast<const uint2*>(res_row0 + nn + k * res_step4));
         }
-        float v[32];
+      };
+      uint2 rnext[8];
+      load_res(0, rnext);
+      // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
+      // column half write identical values to identical addresses; a slot of parity `buf` is rewritten only after
+      // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
+      constexpr int MAXJ = BN / 64;
+      float bpre[MAXJ], gpre[MAXJ];
+#pragma unroll
+      for (int j = 0; j < MAXJ; ++j) {
+        const int col = (hsel + 2 * j) * 32 + lane;
+        const int nb = c.n0 + col, ng = c.n0 + BN / 2 + col;
+        bpre[j] = (sg.bias && j < n_my && nb < sg.N) ? __ldg(sg.bias + nb) : 0.f;
+        gpre[j] = (geglu && sg.bias && j < n_my && ng < sg.N) ? __ldg(sg.bias + ng) : 0.f;
+      }
+
+      mbar_wait(&tfull[buf], (it >> 1) & 1);
+      tc_fence_after();
+      if (n_my == 0) {                           // nothing to store from this warp (N tail): release the accumulator
+        tc_fence_before();
+        tempty_arrive(buf);
+        continue;
+      }
+#pragma unroll
+      for (int j = 0; j < MAXJ; ++j) {
+        if (j < n_my) {
+          sbias[(hsel + 2 * j) * 32 + lane] = bpre[j];
+          if (geglu) sbias[BN / 2 + (hsel + 2 * j) * 32 + lane] = gpre[j];
+        }
+      }
+      __syncwarp();
+      float v[32];
+      tmem_ld32(tmem_acc + lane_addr + hsel * 32, v);   // chunk j+1 is fetched under phase B of chunk j
+#pragma unroll 1
+      for (int ch = 0; ch < n_my; ++ch) {
+        const int c32 = hsel + 2 * ch;           // 32-column chunk index among the tile's OUTPUT columns
         if (geglu) {
           float g[32];
-          tmem_ld32(tmem_acc + lane_addr + c32 * 32, v);
           tmem_ld32(tmem_acc + lane_addr + BN / 2 + c32 * 32, g);
-          tmem_ld_wait();
+          tmem_ld_wait32(v);
+          tmem_ld_wait32(g);
           const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32);
           const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32);
 #pragma unroll
@@ -422,8 +455,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             v[4 * u + 3] = (v[4 * u + 3] + a4.w) * gelu_erf_f(g[4 * u + 3] + g4.w) * alpha;
           }
         } else {
-          tmem_ld32(tmem_acc + lane_addr + c32 * 32, v);
-          tmem_ld_wait();
+          tmem_ld_wait32(v);
           const float4* b4 = reinterpret_cast<const float4*>(sbias + c32 * 32);
           if (plain) {
 #pragma unroll
@@ -464,31 +496,31 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             }
           }
         }
-        if (ch == nchunk - 1) {
+        if (ch == n_my - 1) {
           tc_fence_before();
           tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+2 into it
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u)
           *reinterpret_cast<float4*>(srow + ((u ^ (lane & 7)) << 2)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+        if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + 2) * 32, v);
         __syncwarp();
 
         const int n = out_n0 + c32 * 32 + unit * 4;
+        uint2 rr[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) rr[k] = rnext[k];
+        load_res(ch + 1, rnext);
         if (vec_ok) {
           if (n < out_N) {
-            const bool has_res = sg.res != nullptr;
             const size_t row0 = (size_t)(c.m0 + q * 32 + sub);
-            const bf16* resp = has_res ? sg.res + row0 * sg.res_ld + sg.res_col + n : nullptr;
-            const size_t res_step = (size_t)4 * sg.res_ld, out_step = (size_t)4 * sg.out_ld;
+            const size_t out_step = (size_t)4 * sg.out_ld;
             const size_t out_off = row0 * sg.out_ld + sg.out_col + n;
             float4 f[8];
-            uint2 rr[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
               const int r = k * 4 + sub;         // row within the warp's 32
               f[k] = *reinterpret_cast<const float4*>(wstage + r * 32 + ((unit ^ (r & 7)) << 2));
-              rr[k] = make_uint2(0u, 0u);
-              if (has_res && k * 4 < rows_left) rr[k] = __ldg(reinterpret_cast<const uint2*>(resp + k * res_step));
             }
             if (sg.out_fp32) {
               float* op = reinterpret_cast<float*>(sg.out) + out_off;

@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_metrics.py -x -q -s -m gpu > gpurun_out/metrics.log 2>&1; echo "rc=$?"; grep -E "parity|passed|failed|Error|error|assert" gpurun_out/metrics.log | head -20
-timeout 900 python -m pytest tests/test_gpu_e2e.py tests/test_gpu_norm_elem.py -x -q -m gpu 2>&1 | tail -3
+timeout 900 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_pair_misc.py tests/test_gpu_models.py -x -q -m gpu 2>&1 | tail -3
+ITERS=7 timeout 300 python tools/gemm_bench.py "gemm" 2>&1 | grep gemm
+python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; echo "stage rc=$?"; grep -E "tiles=" gpurun_out/stage.log
