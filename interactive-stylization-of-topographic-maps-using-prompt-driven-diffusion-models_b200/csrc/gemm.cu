@@ -409,7 +409,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
       // column half write identical values to identical addresses; a slot of parity `buf` is rewritten only after
       // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
-      constexpr int MAXJ = BN / 64;
+      constexpr int MAXJ = (BN / 32 + 1) / 2;
       float bpre[MAXJ], gpre[MAXJ];
 #pragma unroll
       for (int j = 0; j < MAXJ; ++j) {
@@ -627,7 +627,7 @@ static bool pair_enabled() {
 template <int BN, int RPAD, int STAGES, bool CONV>
 static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
-  static_assert((BN == 128 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad) or 256 (no LoRA)");
+  static_assert((BN == 128 || BN == 160 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad), 160 / 256 (no LoRA)");
   auto kfn = gemm_kernel<BN, RPAD, STAGES, CONV>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -686,6 +686,18 @@ static int pick_bn(int m_tiles, int N, int r_pad, int n_seg, int act) {
   return tiles256 >= 2 * sm_count() ? 256 : 128;
 }
 
+// N = 320 (the whole 64x64 UNet level) splits into two full 160-wide tiles instead of 256 + a 64-wide tail whose UMMA is
+// bound by the A-operand fetch (N = 64 runs at half rate) and which reloads all of A for a quarter of the columns.
+// TOPO_BN160=0 disables (A/B runs).
+static bool use_bn160(int N, int r_pad, int n_seg, int act) {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TOPO_BN160");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1 && n_seg == 1 && r_pad == 0 && act != TOPO_ACT_GEGLU && (N == 320 || N == 160);
+}
+
 static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int BN, int box_n = 0) {
   TOPO_CHECK(s.W && s.out, TOPO_E_INVAL, "topo_linear_t: W/out must be non-null");
   TOPO_CHECK(s.r_pad == 0 || s.r_pad == 16 || s.r_pad == 32, TOPO_E_INVAL, "r_pad must be 0, 16 or 32 (got %d)", s.r_pad);
@@ -732,7 +744,10 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   TOPO_CHECK(K % BK == 0 && K > 0, TOPO_E_INVAL, "K (%d) must be a positive multiple of 64", K);
   TOPO_CHECK(x_ld % 8 == 0, TOPO_E_INVAL, "x_ld must be a multiple of 8 elements");
   TOPO_CHECK(M > 0, TOPO_E_INVAL, "M must be positive");
-  const int BN = pick_bn((M + BM - 1) / BM, segs[0].N, segs[0].r_pad, n_seg, segs[0].act);
+  int BN = pick_bn((M + BM - 1) / BM, segs[0].N, segs[0].r_pad, n_seg, segs[0].act);
+  // measured: the short-K projections gain 8 % (98 -> 90 us at K = 320 / 384); K = 1280 and the 3x3 convs do not
+  // (convs lose 5 %), so only K < 1024 GEMMs take the 160-wide tile
+  if (use_bn160(segs[0].N, segs[0].r_pad, n_seg, segs[0].act) && K < 1024 && (M + BM - 1) / BM >= sm_count()) BN = 160;
   GemmParams p;
   memset(&p, 0, sizeof(p));
   uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -761,6 +776,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   for (int i = 0; i < n_seg; ++i) p.total_tiles += p.seg[i].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
   if (pair) return launch_gemm_pair<256, 6, false>(p, st);
+  if (BN == 160) return launch_gemm<160, 0, 5, false>(p, grid, st);
   // BN = 256: a fourth stage (192 KB in flight) pays when the K loop is long (latency bound: 3 -> 4 stages took the
   // 3x3 convs from 930 to 1010-1380 TFLOP/s); short-K projections are epilogue bound and keep 3 stages
   if (BN == 256) return K >= 1024 ? launch_gemm<256, 0, 4, false>(p, grid, st) : launch_gemm<256, 0, 3, false>(p, grid, st);
