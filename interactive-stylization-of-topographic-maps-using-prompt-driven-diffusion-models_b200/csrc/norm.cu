@@ -23,13 +23,12 @@ __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
 // Thread -> FIXED channel vector (so sums stay in registers): the block is cut into `rows` pixel lanes of `vpr`
 // threads (rows = 256 / vpr; threads beyond rows*vpr idle); for vpr > 256 the channel range is walked in chunks.
 // 4 independent 16-byte loads in flight per thread.
+// DETERMINISTIC and BATCH-INVARIANT: ppb depends on (HW, C) only, every thread owns its own smem slots (no atomics),
+// and the slots / channels / slabs are folded in a fixed order, so a sample's statistics are the same bits whatever
+// batch it is part of (the CFG shared-prefix path relies on it: tools/batch_invariance.py).
 __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __restrict__ x, int x_ld, int HW, int C, int G,
                                                              int ppb, float* __restrict__ ws) {
-  extern __shared__ float sh[];  // [2*C] per-channel sum, sumsq
-  float* ch_sum = sh;
-  float* ch_sq = sh + C;
-  for (int i = threadIdx.x; i < 2 * C; i += GN_THREADS) sh[i] = 0.f;
-  __syncthreads();
+  extern __shared__ float sh[];  // [rows][2][C]: per pixel-lane, per-channel sum | sumsq
   const int b = blockIdx.y, split = blockIdx.x;
   const int vpr = C >> 3;  // 16-byte vectors per pixel row
   const int p0 = split * ppb;
@@ -39,6 +38,8 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
   const int rows = GN_THREADS / lanes;                     // pixel rows processed in parallel
   const int prow = threadIdx.x / lanes;
   if (prow < rows) {
+    float* my_sum = sh + (size_t)prow * 2 * C;
+    float* my_sq = my_sum + C;
     for (int v = threadIdx.x % lanes; v < vpr; v += lanes) {
       float s[8], q[8];
 #pragma unroll
@@ -68,21 +69,32 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
           q[i] = fmaf(f[i], f[i], q[i]);
         }
       }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        atomicAdd(&ch_sum[v * 8 + i], s[i]);
-        atomicAdd(&ch_sq[v * 8 + i], q[i]);
-      }
+      *reinterpret_cast<float4*>(my_sum + v * 8) = make_float4(s[0], s[1], s[2], s[3]);
+      *reinterpret_cast<float4*>(my_sum + v * 8 + 4) = make_float4(s[4], s[5], s[6], s[7]);
+      *reinterpret_cast<float4*>(my_sq + v * 8) = make_float4(q[0], q[1], q[2], q[3]);
+      *reinterpret_cast<float4*>(my_sq + v * 8 + 4) = make_float4(q[4], q[5], q[6], q[7]);
     }
   }
   __syncthreads();
   const int cpg = C / G;
-  for (int g = threadIdx.x; g < G; g += GN_THREADS) {
-    float s = 0.f, q = 0.f;
-    for (int i = 0; i < cpg; ++i) {
-      s += ch_sum[g * cpg + i];
-      q += ch_sq[g * cpg + i];
+  // 8 threads per group: thread j folds pixel lanes j, j+8, ... (channels in order), then a fixed shuffle tree
+  const int g = threadIdx.x >> 3, j = threadIdx.x & 7;
+  float s = 0.f, q = 0.f;
+  if (g < G) {
+    for (int r = j; r < rows; r += 8) {
+      const float* rs = sh + (size_t)r * 2 * C + g * cpg;
+      for (int i = 0; i < cpg; ++i) {
+        s += rs[i];
+        q += rs[C + i];
+      }
     }
+  }
+#pragma unroll
+  for (int o = 4; o; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (g < G && j == 0) {
     float* o = ws + (((size_t)b * gridDim.x + split) * G + g) * 2;
     o[0] = s;
     o[1] = q;
@@ -101,18 +113,28 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const bf16* __rest
   float* mr = sh + 2 * C;
   const int b = blockIdx.y;
   const int cpg = C / G;
-  for (int g = threadIdx.x; g < G; g += GN_THREADS) {
+  {  // fold the slab partials: 8 threads per group (slabs j, j+8, ... in order), then a fixed shuffle tree
+    const int g = threadIdx.x >> 3, j = threadIdx.x & 7;
     float s = 0.f, q = 0.f;
-    for (int k = 0; k < nsplit_stats; ++k) {
-      const float* w = ws + (((size_t)b * nsplit_stats + k) * G + g) * 2;
-      s += w[0];
-      q += w[1];
+    if (g < G) {
+      for (int k = j; k < nsplit_stats; k += 8) {
+        const float2 w = __ldg(reinterpret_cast<const float2*>(ws + (((size_t)b * nsplit_stats + k) * G + g) * 2));
+        s += w.x;
+        q += w.y;
+      }
     }
-    const float n = (float)HW * cpg;
-    const float mean = s / n;
-    const float var = fmaxf(q / n - mean * mean, 0.f);
-    mr[2 * g] = mean;
-    mr[2 * g + 1] = rsqrtf(var + eps);
+#pragma unroll
+    for (int o = 4; o; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    if (g < G && j == 0) {
+      const float n = (float)HW * cpg;
+      const float mean = s / n;
+      const float var = fmaxf(q / n - mean * mean, 0.f);
+      mr[2 * g] = mean;
+      mr[2 * g + 1] = rsqrtf(var + eps);
+    }
   }
   __syncthreads();
   for (int ch = threadIdx.x; ch < C; ch += GN_THREADS) {
@@ -171,20 +193,42 @@ static int gn_splits(int B, int HW) {
   return s;
 }
 
+// pixels per statistics slab: a function of (HW, C) ONLY (never of the batch), ~80 KB of activations per block
+static int gn_stats_ppb(int HW, int C) {
+  int ppb = 16;
+  while (ppb * 2 * C * 2 <= 81920) ppb *= 2;
+  // at most 64 slabs per sample: short-lived 256 KB blocks cost the 512x512 VAE levels 20 % (measured)
+  const int min_ppb = (HW + 63) / 64;
+  if (ppb < min_ppb) ppb = min_ppb;
+  if (ppb > HW) ppb = HW;
+  return ppb;
+}
+
 int groupnorm_ws_floats(int B, int G) { return B * G * 2 * GN_MAX_SPLITS; }
 
 int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int B, int HW,
                        int C, int G, float eps, int apply_silu, float* ws, cudaStream_t st) {
   TOPO_CHECK(C % 8 == 0 && C % G == 0 && C <= GN_MAX_C, TOPO_E_INVAL, "groupnorm: C=%d G=%d unsupported", C, G);
+  TOPO_CHECK(G * 8 <= GN_THREADS, TOPO_E_INVAL, "groupnorm: at most %d groups", GN_THREADS / 8);
   TOPO_CHECK(x_ld % 8 == 0 && y_ld % 8 == 0, TOPO_E_INVAL, "groupnorm: leading dims must be multiples of 8");
   TOPO_CHECK(ws != nullptr, TOPO_E_INVAL, "groupnorm: workspace required");
+  const int ppb_s = gn_stats_ppb(HW, C);
+  const int nsplit_s = (HW + ppb_s - 1) / ppb_s;
+  const int vpr = C / 8;
+  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;
+  const int rows = GN_THREADS / lanes;
+  const size_t smem_s = (size_t)rows * 2 * C * sizeof(float);
+  static size_t smem_set = 48 * 1024;
+  if (smem_s > smem_set) {
+    TOPO_CUDA(cudaFuncSetAttribute(gn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
+    smem_set = smem_s;
+  }
+  gn_stats_kernel<<<dim3(nsplit_s, B), GN_THREADS, smem_s, st>>>(reinterpret_cast<const bf16*>(x), x_ld, HW, C, G, ppb_s, ws);
   const int splits = gn_splits(B, HW);
   const int ppb = (HW + splits - 1) / splits;
   const int nsplit = (HW + ppb - 1) / ppb;
-  dim3 grid(nsplit, B);
-  gn_stats_kernel<<<grid, GN_THREADS, 2 * C * sizeof(float), st>>>(reinterpret_cast<const bf16*>(x), x_ld, HW, C, G, ppb, ws);
-  gn_apply_kernel<<<grid, GN_THREADS, (2 * C + 2 * G) * sizeof(float), st>>>(
-      reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), y_ld, HW, C, G, ppb, nsplit, ws, gamma, beta,
+  gn_apply_kernel<<<dim3(nsplit, B), GN_THREADS, (2 * C + 2 * G) * sizeof(float), st>>>(
+      reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), y_ld, HW, C, G, ppb, nsplit_s, ws, gamma, beta,
       eps, apply_silu);
   TOPO_CUDA(cudaGetLastError());
   return 0;

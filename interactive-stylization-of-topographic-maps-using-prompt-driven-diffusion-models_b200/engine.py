@@ -449,6 +449,36 @@ def run_layers(layers, h: torch.Tensor, B: int, H: int, W: int, emb, kv_iter, ds
     return h, H, W
 
 
+def _shareable(layers) -> bool:
+    return (len(layers) == 2 and isinstance(layers[0], PRes) and isinstance(layers[1], PST) and len(layers[1].blocks) >= 1
+            and getattr(layers[1].blocks[0].attn1.module, "control_states", None) is None)
+
+
+def run_first_block_shared(layers, h_full: torch.Tensor, Bs: int, rep: int, H: int, W: int, emb: torch.Tensor, kv_iter):
+    """``input_blocks[1]`` = [ResBlock, SpatialTransformer] when the batch is ``rep`` identical copies of ``Bs`` latents
+    that differ only in their cross-attention context (the batched CFG call: ``x_in = cat([x] * 2)``, ``t_in = cat([t] *
+    2)``, ldm ``p_sample_ddim``).  Nothing before the first cross-attention sees the context, so the ResBlock, GroupNorm,
+    ``proj_in``, LayerNorm, q/k/v projection, the 4096-token SELF-attention and its out-projection run once on ``Bs``
+    samples; their result is repeated along the batch and the rest of the block runs on all ``rep * Bs``.  Bit-identical
+    to the duplicated computation (every kernel is deterministic and per-sample)."""
+    res, st = layers
+    M = Bs * H * W
+    r = run_res(res, h_full[:M], Bs, H, W, emb[:Bs])
+    kvs = next(kv_iter)
+    h = gemm(gn(r, Bs, st.norm, False), st.proj_in)
+    b0 = st.blocks[0]
+    h = run_attn(b0.attn1, ln(h, b0.n1), h, Bs, None)
+    h, r = h.repeat(rep, 1), r.repeat(rep, 1)
+    _count(2)
+    Be = Bs * rep
+    h = run_attn(b0.attn2, ln(h, b0.n2), h, Be, kvs[0])
+    g = gemm(ln(h, b0.n3), b0.ff0, act=ACT_GEGLU)
+    h = gemm(g, b0.ff2, res=h)
+    for blk, kv in zip(st.blocks[1:], kvs[1:]):
+        h = run_block(blk, h, Be, kv)
+    return gemm(h, st.proj_out, res=r)
+
+
 def _block_out_channels(layers) -> int:
     return [l.cout for l in layers if isinstance(l, PRes)][-1]
 
@@ -461,6 +491,7 @@ class Prepared:
     unet_kv: list
     cnet_kv: list
     hint_feat: Optional[torch.Tensor]
+    hint_rep: int = 1                     # the hint feature is this many copies of its first Be / hint_rep samples
 
 
 def fingerprint(model: nn.Module) -> Tuple:
@@ -528,14 +559,15 @@ class TopoEngine:
         Be = ctx.shape[0]
         ctx2 = ctx.reshape(-1, ctx.shape[-1]).to(BF16).contiguous()
         key = (ctx.data_ptr(), tuple(ctx.shape), None if hint is None else (hint.data_ptr(), tuple(hint.shape)))
-        feat = None
+        feat, hint_rep = None, 1
         if hint is not None:
             feat = self._hint(hint)
             if hint.shape[0] != Be:
                 if Be % hint.shape[0]:
                     raise capi.TopoError(f"prepare: hint batch {hint.shape[0]} does not divide the context batch {Be}")
-                feat = feat.repeat(Be // hint.shape[0], 1, 1, 1)
-        return Prepared(key, self._kv(self.unet, ctx2, Be), self._kv(self.cnet, ctx2, Be), feat)
+                hint_rep = Be // hint.shape[0]
+                feat = feat.repeat(hint_rep, 1, 1, 1)
+        return Prepared(key, self._kv(self.unet, ctx2, Be), self._kv(self.cnet, ctx2, Be), feat, hint_rep)
 
     def _time(self, net: PNet, t: torch.Tensor) -> torch.Tensor:
         e = ops.timestep_embedding(t, net.mc)
@@ -548,8 +580,11 @@ class TopoEngine:
     @torch.no_grad()
     def apply_model(self, x: torch.Tensor, t: torch.Tensor, ctx: torch.Tensor, hint: Optional[torch.Tensor],
                     control_scales: Sequence[float], only_mid_control: bool = False,
-                    prepared: Optional[Prepared] = None) -> torch.Tensor:
-        """eps [Be,4,H,W] fp32 = UNet(x, t, ctx, control = scales * ControlNet(x, hint, t, ctx))  (SURVEY.md u1-u3)."""
+                    prepared: Optional[Prepared] = None, x_rep: int = 1) -> torch.Tensor:
+        """eps [Be,4,H,W] fp32 = UNet(x, t, ctx, control = scales * ControlNet(x, hint, t, ctx))  (SURVEY.md u1-u3).
+        ``x_rep = k`` is the caller's promise that ``x`` and ``t`` are k identical copies of their first ``Be / k``
+        entries (the batched CFG call): the context-free prefix of both networks then runs once per latent
+        (``run_first_block_shared``)."""
         if not x.is_cuda:
             raise capi.TopoError("apply_model: x must be a CUDA tensor (no CPU fallback)")
         P = prepared if prepared is not None else self.prepare(ctx, hint)
@@ -565,8 +600,13 @@ class TopoEngine:
         h = run_convin(U.input_blocks[0][0], x4).view(Be * H0 * W0, -1)
         H, W = H0, W0
         hs, dims = [h], [(H, W)]
-        for blk in U.input_blocks[1:]:
-            h, H, W = run_layers(blk, h, Be, H, W, emb, kv)
+        if x_rep > 1 and Be % x_rep:
+            raise capi.TopoError(f"apply_model: x_rep={x_rep} does not divide the batch {Be}")
+        for bi, blk in enumerate(U.input_blocks[1:]):
+            if bi == 0 and x_rep > 1 and _shareable(blk):
+                h = run_first_block_shared(blk, h, Be // x_rep, x_rep, H, W, emb, kv)
+            else:
+                h, H, W = run_layers(blk, h, Be, H, W, emb, kv)
             hs.append(h)
             dims.append((H, W))
         h_mid, Hm, Wm = run_layers(U.middle, h, Be, H, W, emb, kv)
@@ -584,7 +624,9 @@ class TopoEngine:
             hc = run_convin(Cn.input_blocks[0][0], x4, add=P.hint_feat).view(Be * H0 * W0, -1)
             H, W = H0, W0
             for i, blk in enumerate(Cn.input_blocks):
-                if i:
+                if i == 1 and x_rep > 1 and P.hint_rep == x_rep and _shareable(blk):   # same latents AND same hints
+                    hc = run_first_block_shared(blk, hc, Be // x_rep, x_rep, H, W, embc, kvc)
+                elif i:
                     hc, H, W = run_layers(blk, hc, Be, H, W, embc, kvc)
                 j = nb - 1 - i
                 if only_mid_control:
@@ -797,7 +839,7 @@ class GraphedModel:
 
     def __init__(self, eng: TopoEngine, Be: int, lat_hw: Tuple[int, int], ctx_shape: Tuple[int, int],
                  hint_hw: Optional[Tuple[int, int]], control_scales: Sequence[float], only_mid_control: bool,
-                 hint_batch: Optional[int] = None):
+                 hint_batch: Optional[int] = None, x_rep: int = 1):
         dev = eng.device
         self.eng = eng
         self.x = torch.zeros(Be, 4, *lat_hw, device=dev)
@@ -810,7 +852,7 @@ class GraphedModel:
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):  # warm-up outside capture: function attributes, workspaces, lazy inits
             P = eng.prepare(self.ctx, self.hint)
-            eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=P)
+            eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=P, x_rep=x_rep)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         n0 = LAUNCHES[0]
@@ -821,7 +863,8 @@ class GraphedModel:
         n0 = LAUNCHES[0]
         self.g_step = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.g_step, pool=self.g_prep.pool()):
-            self.eps = eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=self.P)
+            self.eps = eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=self.P,
+                                       x_rep=x_rep)
         self.step_launches = LAUNCHES[0] - n0
 
     def set_cond(self, ctx: torch.Tensor, hint: Optional[torch.Tensor]) -> None:
@@ -839,12 +882,13 @@ class GraphedModel:
 
 
 def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control,
-             hint_batch=None) -> GraphedModel:
+             hint_batch=None, x_rep=1) -> GraphedModel:
     key = (Be, hint_batch or Be, tuple(lat_hw), tuple(ctx_shape), None if hint_hw is None else tuple(hint_hw),
-           tuple(float(s) for s in control_scales), bool(only_mid_control))
+           tuple(float(s) for s in control_scales), bool(only_mid_control), int(x_rep))
     cache = self.__dict__.setdefault("_graphs", {})
     if key not in cache:
-        cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control, hint_batch)
+        cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control, hint_batch,
+                                  x_rep)
     return cache[key]
 
 

@@ -93,7 +93,7 @@ class DDIMSampler:
             for ctx, hint in conds:
                 # the hacked variant needs two sets of static buffers: distinct graphs for the two branches
                 g = eng.graphed(ctx.shape[0], (H, W), tuple(ctx.shape[1:]), None if hint is None else tuple(hint.shape[2:]),
-                                scales, omc, None if hint is None else hint.shape[0]) if len(conds) == 1 else GraphedModel(
+                                scales, omc, None if hint is None else hint.shape[0], rep) if len(conds) == 1 else GraphedModel(
                                     eng, ctx.shape[0], (H, W), tuple(ctx.shape[1:]),
                                     None if hint is None else tuple(hint.shape[2:]), scales, omc)
                 g.set_cond(ctx, hint)
@@ -116,7 +116,7 @@ class DDIMSampler:
             else:
                 t = torch.full((batch_size * rep,), int(ts[i]), device=dev, dtype=torch.long)
                 xin = img if rep == 1 else torch.cat([img] * rep)
-                outs = [eng.apply_model(xin, t, c_, h_, scales, omc, prepared=P) for c_, h_, P in plans]
+                outs = [eng.apply_model(xin, t, c_, h_, scales, omc, prepared=P, x_rep=rep) for c_, h_, P in plans]
                 eps = outs[0] if len(outs) == 1 else torch.cat(outs)
             sig = float(self.ddim_sigmas[i])
             noise = torch.randn_like(img) if sig != 0.0 else None  # sigma = 0 (eta = 0) on every reference call

@@ -185,3 +185,30 @@ def test_vae_encode_and_validate_step():
     print(f"[parity] validate_step eps-MSE: ours={ours:.6f} oracle={want:.6f} (with encoder+sampled posterior: {full:.6f})")
     assert abs(ours - want) <= 2e-2 * abs(want)
     assert full == full and full > 0
+
+
+@pytest.mark.parametrize("variant", ["ctrlora", "stock"])
+def test_cfg_shared_prefix_is_exact(variant):
+    """The batched CFG call (x_in = cat([x]*2), same hints): running the context-free prefix of both networks once per
+    latent (x_rep=2, deduplicated hint) must reproduce the duplicated computation."""
+    model = synth.build_model(variant, with_vae=False).cuda()
+    eng = model.engine()
+    B, lat = 2, 16
+    hint, ctx, x = synth.make_hint(B, lat * 8).cuda(), synth.make_ctx(B).cuda(), synth.make_xT(B, lat).cuda()
+    c2 = torch.cat([torch.zeros_like(ctx), ctx])
+    x2, h2 = torch.cat([x, x]), torch.cat([hint, hint])
+    t2 = torch.full((2 * B,), 321.0, device="cuda")
+    with torch.no_grad():
+        full = eng.apply_model(x2, t2, c2, h2, model.control_scales, False)
+        again = eng.apply_model(x2, t2, c2, h2, model.control_scales, False)
+        print(f"[parity] run-to-run max|diff| = {(again - full).abs().max().item():.3e}")
+        P = eng.prepare(c2, hint)                                    # one hint per latent
+        shared = eng.apply_model(x2, t2, c2, hint, model.control_scales, False, prepared=P, x_rep=2)
+        P2 = eng.prepare(c2, h2)                                     # hints not deduplicated: only the UNet prefix is shared
+        half = eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P2, x_rep=2)
+    d1 = (shared - full).abs().max().item()
+    d2 = (half - full).abs().max().item()
+    print(f"[parity] CFG shared prefix {variant}: max|shared - duplicated| = {d1:.3e}, UNet-only = {d2:.3e}, "
+          f"max|eps| = {full.abs().max().item():.3e}")
+    assert d1 == 0.0 and d2 == 0.0
+    assert not torch.equal(full[:B], full[B:])                       # the halves do differ (different contexts)

@@ -15,11 +15,11 @@ ctx = synth.make_ctx(B).to(dev); hint = synth.make_hint(B).to(dev); xT = synth.m
 c2 = torch.cat([torch.zeros_like(ctx), ctx]); h2 = torch.cat([hint, hint]); x2 = torch.cat([xT, xT])
 t2 = torch.full((Be,), 501.0, device=dev)
 with torch.no_grad():
-    P = eng.prepare(c2, h2)
-    eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P)
+    P = eng.prepare(c2, hint)   # one hint per tile (the CFG halves share it), context-free prefix shared (x_rep=2)
+    eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStart()
-    eps = eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P)
+    eps = eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStop()
 print("ok", float(eps.abs().mean()))

@@ -14,7 +14,8 @@ model = synth.build_model("ctrlora", control_lora_rank=16).to(dev)
 eng = model.engine()
 hints, ctx, xT = synth.make_hint(T, 512).to(dev), synth.make_ctx(T).to(dev), synth.make_xT(T, 64).to(dev)
 c2 = torch.cat([torch.zeros_like(ctx), ctx]); h2 = torch.cat([hints, hints]); x2 = torch.cat([xT, xT])
-g = eng.graphed(2 * T, (64, 64), tuple(ctx.shape[1:]), (512, 512), model.control_scales, False, T)
+XREP = int(os.environ.get("XREP", "2"))   # 2: the sampler's batched CFG call (context-free prefix shared)
+g = eng.graphed(2 * T, (64, 64), tuple(ctx.shape[1:]), (512, 512), model.control_scales, False, T, XREP)
 
 
 def ev():
@@ -56,12 +57,12 @@ for (kind, tag), d in sorted(rows.items(), key=lambda kv: -kv[1][1])[:25]:
     print(f"  {d[1]:8.3f} ms n={d[0]:3d} {kind:15s} {tag:40s} {d[2] / 1e9 / max(d[1], 1e-9):7.1f} TF/s {d[3] / 1e6 / max(d[1], 1e-9):7.1f} GB/s")
 
 # the same per-shape table for one apply_model
-P = eng.prepare(c2, h2)
+P = eng.prepare(c2, hints)
 t2 = torch.full((2 * T,), 501.0, device=dev)
-eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P)
+eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=XREP)
 torch.cuda.synchronize()
 E.PROF.recs, E.PROF.on = [], True
-eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P)
+eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=XREP)
 torch.cuda.synchronize()
 E.PROF.on = False
 rows, tot = {}, 0.0
