@@ -32,6 +32,7 @@ constexpr int MAX_SEG = 3;
 
 struct alignas(64) GemmSegDev {
   CUtensorMap tm_w;   // [N, taps*K]   box (64, BN)        SW128
+  CUtensorMap tm_w2;  // BN = 320 pair tiles only: box (64, 32) for each CTA's half of the 64-column second MMA
   CUtensorMap tm_la;  // [r_pad, K]    box (64, r_pad)     SW128
   CUtensorMap tm_lb;  // [N, r_pad]    box (r_pad, BN)     SW(r_pad*2)
   const float* bias;
@@ -168,6 +169,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   const int kc = p.K / BK;
   const int num_kb = p.taps * kc;
   constexpr uint32_t TMEM_COLS = 512;
+  // BN = 320 (pair only): ONE 320-column accumulator filled by two UMMAs per K step (N = 256 at column 0, N = 64 at column
+  // 256) from a single A stage, so the N = 320 level loads A once instead of once per n tile; no accumulator double
+  // buffering (2 x 320 > 512 columns), which a 45..135-block K loop hardly notices
+  constexpr int NBUF = BN > 256 ? 1 : 2;
+  static_assert(BN <= 256 || (PAIR && BN == 320 && RPAD == 0), "BN = 320 exists as a CTA-pair kernel only");
   constexpr uint32_t T_COL = 2 * BN;
 
   if (warp == 0 && lane == 0) {
@@ -236,7 +242,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             } else {
               tma2_load_2d(a_s, &p.tm_x, fb, kb * BK, c.m0);
             }
-            tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * (n_eff / 2));  // this CTA's half of the W rows
+            if constexpr (BN == 320) {   // rows [rank*128, +128) of the 256-wide part, rows [256 + rank*32, +32) of the 64-wide part
+              tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * 128);
+              tma2_load_2d(w_s + 128 * BK * 2, &sg.tm_w2, fb, kb * BK, c.n0 + 256 + rank * 32);
+            } else {
+              tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * (n_eff / 2));  // this CTA's half of the W rows
+            }
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -269,7 +280,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       uint32_t phase = 0;
       int it = 0;
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
-        const int buf = it & 1;
+        const int buf = NBUF == 2 ? (it & 1) : 0;
+        const uint32_t acc_phase = NBUF == 2 ? ((it >> 1) & 1) : (it & 1);
         const uint32_t tmem_acc = tmem_base + buf * BN;
         const uint32_t tmem_t = tmem_base + T_COL;
         // the last N tile of a segment only multiplies the columns that exist (UMMA N is a run-time field, multiple of 16)
@@ -277,7 +289,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         const int n_left = p.seg[c.seg].N - c.n0;
         const uint32_t n_eff = n_left >= BN ? BN : (PAIR ? ((n_left + 31) & ~31) : ((n_left + 15) & ~15));
         const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, n_eff);
-        mbar_wait(&tempty[buf], ((it >> 1) & 1) ^ 1);  // epilogue drained this accumulator (two tiles ago)
+        mbar_wait(&tempty[buf], acc_phase ^ 1);  // epilogue drained this accumulator (NBUF tiles ago)
         tc_fence_after();
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
@@ -288,7 +300,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
-            if (PAIR) umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
+            if constexpr (BN == 320) {
+              umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), make_idesc_bf16(2 * BM, 256), (kb | k) != 0);
+              umma2_bf16(tmem_acc + 256, ad, kmajor_desc(w_s + 128 * BK * 2 + k * 32, 128), make_idesc_bf16(2 * BM, 64), (kb | k) != 0);
+            } else if (PAIR) umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
             else umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
             if (RPAD) umma_bf16(tmem_t, ad, kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
           }
@@ -330,7 +345,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
       const GemmSegDev& sg = p.seg[c.seg];
-      const int buf = it & 1;
+      const int buf = NBUF == 2 ? (it & 1) : 0;
+      const uint32_t acc_phase = NBUF == 2 ? ((it >> 1) & 1) : (it & 1);
       const uint32_t tmem_acc = tmem_base + buf * BN;
       float* sbias = sbias_all + buf * BN;
       // (the bias tile is written per warp after the accumulator wait, see below: no CTA-wide epilogue barrier)
@@ -419,7 +435,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         gpre[j] = (geglu && sg.bias && j < n_my && ng < sg.N) ? __ldg(sg.bias + ng) : 0.f;
       }
 
-      mbar_wait(&tfull[buf], (it >> 1) & 1);
+      mbar_wait(&tfull[buf], acc_phase);
       tc_fence_after();
       if (n_my == 0) {                           // nothing to store from this warp (N tail): release the accumulator
         tc_fence_before();
@@ -627,7 +643,7 @@ static bool pair_enabled() {
 template <int BN, int RPAD, int STAGES, bool CONV>
 static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
-  static_assert((BN == 128 || BN == 160 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad), 160 / 256 (no LoRA)");
+  static_assert((BN == 128 || BN == 160 || BN == 192 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad), 160 / 192 / 256 (no LoRA)");
   auto kfn = gemm_kernel<BN, RPAD, STAGES, CONV>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -695,7 +711,27 @@ static bool use_bn160(int N, int r_pad, int n_seg, int act) {
     const char* e = getenv("TOPO_BN160");
     v = (e && e[0] == '0') ? 0 : 1;
   }
-  return v == 1 && n_seg == 1 && r_pad == 0 && act != TOPO_ACT_GEGLU && (N == 320 || N == 160);
+  static int wide = -1;
+  if (wide < 0) {
+    const char* e = getenv("TOPO_BN160_WIDE");
+    wide = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1 && n_seg == 1 && r_pad == 0 && act != TOPO_ACT_GEGLU && (N == 320 || N == 160 || (wide && N == 640));
+}
+
+// TOPO_BN320=0 disables the single-accumulator 320-wide pair tile (A/B runs)
+static bool bn320_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("TOPO_BN320");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+static bool bn320_force_gemm() {
+  const char* e = getenv("TOPO_BN320");
+  return e && e[0] == '2';
 }
 
 static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int BN, int box_n = 0) {
@@ -707,6 +743,11 @@ static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int 
   uint32_t box[2] = {BK, (uint32_t)(box_n ? box_n : BN)};  // box_n = BN / 2: each CTA of a pair loads half of the W rows
   int rc = make_tmap(&d.tm_w, s.W, 2, dims, strides, box, 128);
   if (rc) return rc;
+  if (BN == 320) {
+    uint32_t box2[2] = {BK, 32};
+    rc = make_tmap(&d.tm_w2, s.W, 2, dims, strides, box2, 128);
+    if (rc) return rc;
+  }
   if (s.r_pad) {
     TOPO_CHECK(s.A && s.B, TOPO_E_INVAL, "LoRA A/B must be non-null when r_pad > 0");
     uint64_t da[2] = {(uint64_t)K, (uint64_t)s.r_pad};
@@ -761,9 +802,13 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   // (measured: K = 1280 / 2560 -> +5 / +9 %, K = 320 GEGLU -> -16 %)
   const bool pair = BN == 256 && r_pad == 0 && K >= 1024 && pair_enabled() &&
                     ((M + 2 * BM - 1) / (2 * BM)) >= sm_count() / 2;
+  // the 320-wide single-accumulator tile pays on the 45+-block K loops of the convs (273 -> 247 us) but not here: with
+  // K = 1280 the un-overlapped epilogue costs more than the second A load (152 -> 160 us); TOPO_BN320=2 forces it
+  const bool wide320 = pair && n_seg == 1 && segs[0].N == 320 && segs[0].act != TOPO_ACT_GEGLU && bn320_force_gemm();
+  if (wide320) BN = 320;
   for (int i = 0; i < n_seg; ++i) {
     TOPO_CHECK(segs[i].r_pad == r_pad, TOPO_E_INVAL, "all segments of one call must share r_pad");
-    rc = fill_seg(p.seg[i], segs[i], K, 1, BN, pair ? BN / 2 : 0);
+    rc = fill_seg(p.seg[i], segs[i], K, 1, BN, pair ? (BN == 320 ? 128 : BN / 2) : 0);
     if (rc) return rc;
     maxN = segs[i].N > maxN ? segs[i].N : maxN;
   }
@@ -775,6 +820,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   p.total_tiles = 0;
   for (int i = 0; i < n_seg; ++i) p.total_tiles += p.seg[i].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
+  if (wide320) return launch_gemm_pair<320, 5, false>(p, st);
   if (pair) return launch_gemm_pair<256, 6, false>(p, st);
   if (BN == 160) return launch_gemm<160, 0, 5, false>(p, grid, st);
   // BN = 256: a fourth stage (192 KB in flight) pays when the K loop is long (latency bound: 3 -> 4 stages took the
@@ -797,6 +843,13 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   const int pair_tiles = ((B * H * W + 2 * BM - 1) / (2 * BM)) * ((seg->N + 255) / 256);
   const bool pair = pair_enabled() && seg->N >= 192 && pair_tiles >= 40;
   if (pair) BN = 256;
+  static int bn192 = -1;
+  if (bn192 < 0) {
+    const char* e = getenv("TOPO_BN192");
+    bn192 = (e && e[0] == '1') ? 1 : 0;
+  }
+  if (pair && bn192 && seg->N == 320) BN = 192;   // n tiles 192 + 128 instead of 256 + 64 (measured: no gain)
+  if (pair && !bn192 && seg->N == 320 && bn320_enabled()) BN = 320;
   GemmParams p;
   memset(&p, 0, sizeof(p));
   const int bw = W < BM ? W : BM;
@@ -811,7 +864,7 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   uint32_t box[4] = {BK, (uint32_t)bw, (uint32_t)bh, (uint32_t)bb};
   int rc = make_tmap(&p.tm_x, x, 4, dims, strides, box, 128);
   if (rc) return rc;
-  rc = fill_seg(p.seg[0], *seg, C, 9, BN, pair ? BN / 2 : 0);
+  rc = fill_seg(p.seg[0], *seg, C, 9, BN, pair ? (BN == 320 ? 128 : BN / 2) : 0);
   if (rc) return rc;
   p.M = B * H * W;
   p.K = C;
@@ -828,6 +881,8 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
   p.m_tiles = p.tiles_w * p.tiles_h * tiles_b;
   p.total_tiles = p.seg[0].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
+  if (pair && BN == 320) return launch_gemm_pair<320, 5, true>(p, st);
+  if (pair && BN == 192) return launch_gemm_pair<192, 6, true>(p, st);
   if (pair) return launch_gemm_pair<256, 6, true>(p, st);
   if (BN == 256) return launch_gemm<256, 0, 4, true>(p, grid, st);
   return launch_gemm<128, 0, 6, true>(p, grid, st);

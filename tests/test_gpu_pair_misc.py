@@ -17,7 +17,7 @@ def _ops():
 
 
 @pytest.mark.parametrize("M,K,N", [(20000, 320, 640), (155648, 320, 320), (38912, 640, 2560), (20096, 1280, 1000),
-                                   (9728, 5120, 1280)])
+                                   (9728, 5120, 1280), (40000, 1280, 320), (155648, 1280, 320)])
 def test_pair_gemm(M, K, N):
     ops = _ops()
     x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
@@ -37,7 +37,7 @@ def test_pair_gemm_geglu():
 
 
 @pytest.mark.parametrize("B,H,C,N", [(38, 32, 128, 320), (19, 64, 64, 256), (5, 128, 64, 96), (38, 8, 320, 1280),
-                                     (38, 16, 192, 640)])
+                                     (38, 16, 192, 640), (19, 64, 320, 320), (38, 64, 64, 320)])
 def test_pair_conv3x3(B, H, C, N):
     ops = _ops()
     x = rnd(B, H, H, C, seed=1).to(BF16)

@@ -1,3 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_norm_elem.py -x -q -m gpu 2>&1 | tail -1
-XREP=2 python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; grep -E "tiles=" gpurun_out/stage.log; grep -E "groupnorm" gpurun_out/stage.log
+timeout 900 python -m pytest tests/test_gpu_gemm.py tests/test_gpu_pair_misc.py -x -q -m gpu 2>&1 | tail -1
+TOPO_BN320=2 timeout 900 python -m pytest tests/test_gpu_pair_misc.py -k pair_gemm -x -q -m gpu 2>&1 | tail -1
+for i in 1 2; do XREP=2 python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; grep -E "tiles=" gpurun_out/stage.log; done

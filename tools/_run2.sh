@@ -1,4 +1,2 @@
 mkdir -p gpurun_out
-timeout 120 python tools/pair_check.py 2>&1 | tail -12; echo "check rc=$?"
-timeout 300 python -m pytest tests/test_gpu_gemm.py -m gpu -q -x 2>&1 | tail -2
-ITERS=5 timeout 300 python tools/gemm_bench.py 2>&1 | grep -E "gemm|conv" 
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 3 --warmup 3 > gpurun_out/bench_2gpu.json 2> gpurun_out/bench_2gpu.err; echo "rc=$?"; cut -c1-300 gpurun_out/bench_2gpu.json; tail -3 gpurun_out/bench_2gpu.err
