@@ -33,8 +33,9 @@ WORKLOAD = ("ctrlora (configs[1]): random-init SD1.5-arch UNet+ControlNet, Contr
 GFLOP_APPLY, GFLOP_HOIST, GFLOP_VAE = 1069.4, 14.72 + 4.31, 2514.5
 TFLOP_PER_TILE = (31 * 2 * GFLOP_APPLY + 2 * GFLOP_HOIST + GFLOP_VAE) / 1e3
 # dram__bytes_read.sum + dram__bytes_write.sum per launch (MB), mean over the launches of that class in the
-# `ncu --set full` capture of tools/profile_step.py (same Be=38 apply_model): profiles/r01e_ncu_full_{gemm,attention}.txt
-NCU_TRAFFIC_MB = {"gemm": 196.7, "conv3x3": 131.4, "attn_self": 462.0}
+# `ncu --set full` capture of tools/profile_step.py (same Be=38 apply_model): profiles/r01g_ncu_full_gemm.txt (first 80
+# gemm_kernel launches: 62 projections, 18 convs) and profiles/r01e_ncu_full_attention.txt (Be=38 self-attention)
+NCU_TRAFFIC_MB = {"gemm": 173.2, "conv3x3": 89.3, "attn_self": 462.0}
 
 
 def peaks():
@@ -226,7 +227,7 @@ def run_ours(args):
         roof = {"bound": "tensor" if tensor else "hbm", "kernel": top, "achieved": ach, "peak": peak,
                 "unit": "TFLOP/s" if tensor else "GB/s", "frac": ach / peak,
                 "traffic": NCU_TRAFFIC_MB[top] * 1e6 if top in NCU_TRAFFIC_MB else None,
-                "traffic_source": "ncu --set full, mean DRAM read+write bytes per launch of this class (profiles/r01e_ncu_full_*.txt)",
+                "traffic_source": "ncu --set full, mean DRAM read+write bytes per launch of this class (profiles/r01g_ncu_full_gemm.txt, r01e_ncu_full_attention.txt)",
                 "peak_source": pk["src"] + (" (sustained bf16)" if tensor else " (copy)"),
                 "launches": d["launches"], "avg_launch_us": 1e3 * d["ms"] / d["launches"],
                 "share_of_apply_model": d["ms"] / total,
