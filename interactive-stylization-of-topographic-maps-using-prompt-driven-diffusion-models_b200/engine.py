@@ -449,6 +449,11 @@ def run_layers(layers, h: torch.Tensor, B: int, H: int, W: int, emb, kv_iter, ds
     return h, H, W
 
 
+def _two_streams() -> bool:
+    import os
+    return os.environ.get("TOPO_TWO_STREAMS", "1") != "0"
+
+
 def _shareable(layers) -> bool:
     return (len(layers) == 2 and isinstance(layers[0], PRes) and isinstance(layers[1], PST) and len(layers[1].blocks) >= 1
             and getattr(layers[1].blocks[0].attn1.module, "control_states", None) is None)
@@ -594,6 +599,38 @@ class TopoEngine:
         x4 = ops.nchw_to_nhwc(x)
         _count()
 
+        # -- ControlNet trunk: independent of the UNet encoder until the zero-convs add its outputs to the UNet skips, so it
+        #    is issued on a second stream (a fork/join inside the captured graph): the persistent kernels of the two
+        #    networks fill each other's tails and the SM-starved 8x8 / 16x16 levels.  TOPO_TWO_STREAMS=0: one stream.
+        use_control = P.hint_feat is not None
+
+        def cnet_trunk():
+            embc = self._time(Cn, tf)
+            kvc = iter(P.cnet_kv)
+            hc = run_convin(Cn.input_blocks[0][0], x4, add=P.hint_feat).view(Be * H0 * W0, -1)
+            Hc, Wc = H0, W0
+            outs = []
+            for i, blk in enumerate(Cn.input_blocks):
+                if i == 1 and x_rep > 1 and P.hint_rep == x_rep and _shareable(blk):   # same latents AND same hints
+                    hc = run_first_block_shared(blk, hc, Be // x_rep, x_rep, Hc, Wc, embc, kvc)
+                elif i:
+                    hc, Hc, Wc = run_layers(blk, hc, Be, Hc, Wc, embc, kvc)
+                outs.append(hc)
+            hm, _, _ = run_layers(Cn.middle, hc, Be, Hc, Wc, embc, kvc)
+            return outs, hm
+
+        side, trunk = None, None
+        if use_control:
+            if _two_streams() and not PROF.on:
+                side = self.__dict__.get("_side")
+                if side is None:
+                    side = self.__dict__["_side"] = torch.cuda.Stream(device=x.device)
+                side.wait_stream(torch.cuda.current_stream(x.device))
+                with torch.cuda.stream(side):
+                    trunk = cnet_trunk()
+            else:
+                trunk = cnet_trunk()
+
         # -- UNet encoder + middle
         emb = self._time(U, tf)
         kv = iter(P.unet_kv)
@@ -617,24 +654,17 @@ class TopoEngine:
         cat = [torch.empty(hs[nb - 1 - j].shape[0], ch_in[j] + hs[nb - 1 - j].shape[1], dtype=BF16, device=x.device)
                for j in range(nb)]
 
-        use_control = P.hint_feat is not None
         if use_control:
-            embc = self._time(Cn, tf)
-            kvc = iter(P.cnet_kv)
-            hc = run_convin(Cn.input_blocks[0][0], x4, add=P.hint_feat).view(Be * H0 * W0, -1)
-            H, W = H0, W0
-            for i, blk in enumerate(Cn.input_blocks):
-                if i == 1 and x_rep > 1 and P.hint_rep == x_rep and _shareable(blk):   # same latents AND same hints
-                    hc = run_first_block_shared(blk, hc, Be // x_rep, x_rep, H, W, embc, kvc)
-                elif i:
-                    hc, H, W = run_layers(blk, hc, Be, H, W, embc, kvc)
+            if side is not None:
+                torch.cuda.current_stream(x.device).wait_stream(side)
+            hcs, hc_mid = trunk
+            for i, hc in enumerate(hcs):
                 j = nb - 1 - i
                 if only_mid_control:
                     cat[j][:, ch_in[j]:].copy_(hs[i])
                 else:  # (e) skip + scale*zero_conv(hc) straight into the skip half of concat buffer j
                     gemm(hc, Cn.zero[i], out=cat[j], out_col=ch_in[j], res=hs[i], alpha=float(control_scales[i]))
-            hc, H, W = run_layers(Cn.middle, hc, Be, H, W, embc, kvc)
-            gemm(hc, Cn.mid_out, out=cat[0], out_col=0, res=h_mid, alpha=float(control_scales[len(Cn.zero)]))
+            gemm(hc_mid, Cn.mid_out, out=cat[0], out_col=0, res=h_mid, alpha=float(control_scales[len(Cn.zero)]))
         else:
             for j in range(nb):
                 cat[j][:, ch_in[j]:].copy_(hs[nb - 1 - j])

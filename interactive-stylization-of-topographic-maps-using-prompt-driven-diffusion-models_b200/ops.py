@@ -190,7 +190,7 @@ _gn_ws = {}
 
 def groupnorm_ws(B: int, G: int, device) -> torch.Tensor:
     n = capi.load_library().topo_groupnorm_ws_floats(B, G)
-    key = (str(device), n)
+    key = (str(device), n, capi.stream())   # one workspace per stream: the two networks of a step run concurrently
     if key not in _gn_ws:
         _gn_ws[key] = torch.zeros(n, dtype=torch.float32, device=device)  # the fused kernel's counters start at zero
     return _gn_ws[key]
