@@ -39,12 +39,14 @@ def test_attention(B, heads, Nq, Nk, d):
         assert got[..., d:].abs().max() == 0, "padded head columns must stay zero"
 
 
-def test_attention_peaked_softmax():
-    """Large logits: online max/rescale path must stay exact (no overflow, correct renormalisation)."""
+@pytest.mark.parametrize("gain", [6.0, 60.0, 400.0])
+def test_attention_peaked_softmax(gain):
+    """Large logits: online max/rescale path must stay exact (no overflow, correct renormalisation); gain 60 / 400 make
+    the row maximum jump by hundreds of nats between key blocks."""
     from topo_b200 import ops
     B, heads, N, d, dp = 1, 2, 512, 40, 48
     q, k, v = _mk(B, N, heads, d, dp, 1), _mk(B, N, heads, d, dp, 2), _mk(B, N, heads, d, dp, 3)
-    q = (q.float() * 6).to(BF16)
+    q = (q.float() * gain).to(BF16)
     o = ops.attention(q, k, v, heads, dp, d ** -0.5)
     ref = _ref(q, k, v, heads, d, dp, d ** -0.5)
     assert_close(o.float().reshape(B, N, heads, dp)[..., :d], ref, 3e-2, "attention peaked")
