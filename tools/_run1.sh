@@ -1,4 +1,5 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_attention.py tests/test_gpu_gemm.py tests/test_gpu_pair_misc.py -x -q -m gpu 2>&1 | tail -1
-ITERS=7 timeout 300 python tools/gemm_bench.py "attn" 2>&1 | grep attn
-for i in 1 2; do XREP=2 python tools/stage_breakdown.py > gpurun_out/stage.log 2>&1; grep -E "tiles=" gpurun_out/stage.log; done
+timeout 600 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
+timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -1 gpurun_out/pytest_gpu.log
+timeout 600 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cut -c1-200 gpurun_out/bench.json
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv python tools/profile_step.py > gpurun_out/ncu1.log 2>&1; echo "ncu launches rc=$?"
