@@ -26,7 +26,7 @@ from .capi import ACT_GELU, ACT_NONE, ACT_RELU
 from .engine import Lin, Norm, _dev, gemm, gemm_multi, ln
 from .ops import BF16
 
-__all__ = ["LastStateAdapter", "BERTTextEncoder", "build_text_encoder"]
+__all__ = ["LastStateAdapter", "BERTTextEncoder", "build_text_encoder", "BertAlign", "build_cond_uc_safe_pad"]
 
 
 class LastStateAdapter(nn.Module):
@@ -187,3 +187,60 @@ def build_text_encoder(n_embed: int = 768, n_layer: int = 12, max_len: int = 77,
     hf_bert.eval()
     te = BERTTextEncoder(hf_bert, tokenizer, LastStateAdapter(n_embed, n_embed, adapter_hidden_layers), max_len)
     return te.to(device)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# CLIP (+) BERT context fusion (TextEncoder_Finetuning/token_utils.py:95-158)
+# ----------------------------------------------------------------------------------------------------------------
+def _plain_ln(x2: torch.Tensor) -> torch.Tensor:
+    """``F.layer_norm(x, (C,))`` without affine on bf16 rows ``[M, C]`` (the LayerNorm kernel with gamma = 1, beta = 0)."""
+    C = x2.shape[1]
+    one = torch.ones(C, dtype=torch.float32, device=x2.device)
+    return ln(x2, Norm(one, torch.zeros_like(one), 1e-5))
+
+
+class BertAlign(nn.Module):
+    """``token_utils.py:95-112``: ``sigmoid(beta) * proj(layer_norm(x))`` with a zero-initialised ``proj`` and a scalar
+    gate (``gate_init = -2``) — a light alignment of the BERT tokens only.  Same parameter names (``proj``, ``beta``)."""
+
+    def __init__(self, dim: int = 768, gate_init: float = -2.0):
+        super().__init__()
+        self.proj = nn.Linear(dim, dim, bias=True)
+        nn.init.zeros_(self.proj.weight)
+        nn.init.zeros_(self.proj.bias)
+        self.beta = nn.Parameter(torch.tensor(gate_init))
+
+    @torch.no_grad()
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda:
+            raise capi.TopoError("BertAlign: x must be a CUDA tensor (no CPU forward)")
+        B, T, C = x.shape
+        lin = _lin(self.proj, x.device)
+        y = gemm(_plain_ln(x.reshape(B * T, C).to(BF16).contiguous()), lin, alpha=float(torch.sigmoid(self.beta)))
+        return y.view(B, T, C).float()
+
+
+@torch.no_grad()
+def build_cond_uc_safe_pad(seg, prompts, model, clip_textenc, bert_textenc, device, clip_style_text="map in swisstopo style",
+                           gamma=1.0, w_clip=0.4, bert_align=None, start_idx=8):
+    """``token_utils.py:115-158``: ``cond = w_clip * clip_ctx + gamma * tail(bert)``, ``uc = w_clip * clip_ctx`` — the CFG
+    difference comes from BERT only.  ``clip_textenc`` is any object with ``get_learned_conditioning(list[str]) ->
+    [B,77,768]`` (CLIP weights are outside this package); the BERT tokens are (optionally aligned,) layer-normed without
+    affine and written into the 77-token window from ``start_idx``.  Returns ``(cond, uc)`` with the same hint list."""
+    seg = seg.to(device=device, dtype=torch.float32)
+    B = seg.size(0)
+    clip_ctx = clip_textenc.get_learned_conditioning([clip_style_text] * B).to(device=device, dtype=torch.float32)
+    bert_tok = bert_textenc.encode(prompts).to(device=device, dtype=torch.float32)
+    if bert_align is not None:
+        bert_tok = bert_align(bert_tok)
+    Bb, Lb, C = bert_tok.shape
+    bert_tok = _plain_ln(bert_tok.reshape(Bb * Lb, C).to(BF16).contiguous()).view(Bb, Lb, C).float()
+    max_len = clip_ctx.size(1)
+    tail = torch.zeros(B, max_len, clip_ctx.size(-1), device=device, dtype=torch.float32)
+    end = min(max_len, start_idx + Lb)
+    if end > start_idx:
+        tail[:, start_idx:end, :] = bert_tok[:, :end - start_idx, :]
+    cond_ctx = w_clip * clip_ctx + gamma * tail
+    uc_ctx = w_clip * clip_ctx
+    hints = [seg]
+    return {"c_concat": hints, "c_crossattn": [cond_ctx]}, {"c_concat": hints, "c_crossattn": [uc_ctx]}

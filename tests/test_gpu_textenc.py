@@ -89,3 +89,42 @@ def test_mask_must_be_right_padded():
     mask[0, 2] = 0
     with pytest.raises(TopoError):
         te.encode_ids(ids, mask)
+
+
+def test_bert_align_and_clip_bert_fusion():
+    """token_utils.py:95-158: BertAlign (LN -> zero-init proj -> sigmoid gate) and cond/uc = w_clip*clip (+ gamma*tail)."""
+    import torch.nn.functional as F
+    from topo_b200.textenc import BertAlign, build_cond_uc_safe_pad
+    torch.manual_seed(0)
+    B, Lb, C = 3, 20, 768
+    al = BertAlign(C).cuda()
+    torch.nn.init.normal_(al.proj.weight, std=0.03)
+    torch.nn.init.normal_(al.proj.bias, std=0.1)
+    x = torch.randn(B, Lb, C, device="cuda") * 2 + 0.5
+    got = al(x)
+    ref = torch.sigmoid(al.beta) * F.linear(F.layer_norm(x, (C,)), al.proj.weight, al.proj.bias)
+    rel = (got - ref).abs().max().item() / ref.abs().max().item()
+    print(f"[parity] BertAlign: rel={rel:.3e}")
+    assert rel <= 2e-2
+
+    class Clip:
+        def get_learned_conditioning(self, prompts):
+            g = torch.Generator().manual_seed(1)
+            return torch.randn(len(prompts), 77, C, generator=g).cuda()
+
+    class Bert:
+        def encode(self, prompts):
+            return x[:len(prompts)]
+
+    seg = torch.rand(B, 3, 64, 64)
+    cond, uc = build_cond_uc_safe_pad(seg, ["a", "b", "c"], None, Clip(), Bert(), "cuda", gamma=0.7, w_clip=0.4,
+                                      bert_align=al, start_idx=8)
+    clip = Clip().get_learned_conditioning(["x"] * B)
+    tail = torch.zeros(B, 77, C, device="cuda")
+    tail[:, 8:8 + Lb] = F.layer_norm(ref, (C,))
+    want = 0.4 * clip + 0.7 * tail
+    rel2 = (cond["c_crossattn"][0] - want).abs().max().item() / want.abs().max().item()
+    print(f"[parity] build_cond_uc_safe_pad: rel={rel2:.3e}")
+    assert rel2 <= 3e-2
+    assert torch.equal(uc["c_crossattn"][0], 0.4 * clip) and cond["c_concat"][0] is uc["c_concat"][0]
+    assert cond["c_crossattn"][0].shape == (B, 77, C)

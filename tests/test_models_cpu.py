@@ -85,3 +85,17 @@ def test_text_encoder_containers():
         te.encode(["a prompt"])                                   # no tokenizer
     with pytest.raises(TopoError):
         BERTTextEncoder(BertModel(BertConfig(num_hidden_layers=1, hidden_act="relu"), add_pooling_layer=False))
+
+
+def test_bert_align_container_matches_reference_names():
+    """token_utils.py:95-112: parameters ``proj.weight`` (zeros), ``proj.bias`` (zeros), scalar ``beta`` = gate_init."""
+    import torch
+    from topo_b200 import capi
+    from topo_b200.textenc import BertAlign
+    m = BertAlign(768, gate_init=-2.0)
+    sd = m.state_dict()
+    assert sorted(sd) == ["beta", "proj.bias", "proj.weight"]
+    assert float(sd["beta"]) == -2.0 and float(sd["proj.weight"].abs().max()) == 0.0
+    import pytest
+    with pytest.raises(capi.TopoError):
+        m(torch.zeros(1, 4, 768))
