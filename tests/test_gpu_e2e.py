@@ -212,3 +212,40 @@ def test_cfg_shared_prefix_is_exact(variant):
           f"max|eps| = {full.abs().max().item():.3e}")
     assert d1 == 0.0 and d2 == 0.0
     assert not torch.equal(full[:B], full[B:])                       # the halves do differ (different contexts)
+
+
+def test_eager_pytorch_oracle_timing_column():
+    """the third column of the baseline table — the SAME oracle (the reference's PyTorch formulation:
+    fp32, explicit softmax(QK^T)V, library convs / GEMMs) timed in eager mode on this B200, beside the kernels, on one
+    apply_model at Be = 8 (4 tiles x [uncond; cond], 64x64 latents).  Parity is asserted on the same call; the timing is
+    printed for profiles/ (the oracle is the checker here, the number is context, not a product path)."""
+    from oracle import ldm_oracle as O
+    model = synth.build_model("ctrlora", with_vae=False).cuda()
+    sd = {k: v.float() for k, v in model.state_dict().items()}
+    scales = synth.lora_scales(model)
+    B = 4
+    hint, ctx, x = synth.make_hint(B, 512).cuda(), synth.make_ctx(B).cuda(), synth.make_xT(B, 64).cuda()
+    c2, h2, x2 = torch.cat([torch.zeros_like(ctx), ctx]), torch.cat([hint, hint]), torch.cat([x, x])
+    t2 = torch.full((2 * B,), 501, device="cuda")
+    cond = {"c_crossattn": [c2], "c_concat": [h2]}
+
+    def timed(fn, n):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            out = fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n, out
+
+    eng = model.engine()
+    P = eng.prepare(c2, hint)
+    with torch.no_grad():
+        ms_ref, ref = timed(lambda: O.apply_model(sd, x2, t2, cond, heads=8, scales=scales), 2)
+        ms_k, eps = timed(lambda: eng.apply_model(x2, t2.float(), c2, h2, model.control_scales, False, prepared=P, x_rep=2), 5)
+        torch.backends.cudnn.allow_tf32 = True       # PyTorch's default for convolutions
+        ms_tf32, _ = timed(lambda: O.apply_model(sd, x2, t2, cond, heads=8, scales=scales), 2)
+    cos = _cos(eps, ref)
+    print(f"[timing] apply_model Be=8: eager PyTorch oracle fp32 {ms_ref:.1f} ms (cudnn TF32 convs: {ms_tf32:.1f} ms) | "
+          f"sm_100a kernels {ms_k:.2f} ms (eager launches, no graph) | x{ms_ref / ms_k:.1f} / x{ms_tf32 / ms_k:.1f}; cos={cos:.6f}")
+    assert cos >= 0.9995
