@@ -13,10 +13,27 @@ namespace topo {
 constexpr int GN_THREADS = 256;
 constexpr int GN_MAX_SPLITS = 256;
 constexpr int GN_MAX_C = 4096;
+#ifndef GN_STATS_MINB
+#define GN_STATS_MINB 3
+#endif
+#ifndef GN_APPLY_MINB
+#define GN_APPLY_MINB 5
+#endif
 
 __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
   f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
   f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
+}
+
+// Threads across the channel dimension: the widest divisor vpr/k that is <= 128, so that rows = 256 / lanes pixel rows
+// fill the block (C = 1280: 80 lanes x 3 rows, two vectors per thread, instead of 160 lanes and 96 idle threads;
+// C = 2560: 80 x 3 with four vectors per thread instead of an unbalanced 256-lane walk).  A function of C only.
+__host__ __device__ __forceinline__ int gn_lanes(int vpr) {
+  if (vpr <= 128) return vpr;
+  if (vpr > 256) return (vpr % 2 == 0 && vpr / 2 <= 256) ? vpr / 2 : GN_THREADS;  // C = 2560: 160 x 1 (3 rows = 60 KB of smem)
+  for (int k = 2; k <= 16; ++k)
+    if (vpr % k == 0 && vpr / k <= 128) return vpr / k;
+  return vpr;
 }
 
 // grid (splits, B). Block handles pixels [split*ppb, min(HW, (split+1)*ppb)) of sample b.
@@ -26,15 +43,20 @@ __device__ __forceinline__ void unpack8(const uint4& u, float* f) {
 // DETERMINISTIC and BATCH-INVARIANT: ppb depends on (HW, C) only, every thread owns its own smem slots (no atomics),
 // and the slots / channels / slabs are folded in a fixed order, so a sample's statistics are the same bits whatever
 // batch it is part of (the CFG shared-prefix path relies on it: tools/batch_invariance.py).
-__global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __restrict__ x, int x_ld, int HW, int C, int G,
-                                                             int ppb, float* __restrict__ ws) {
+__global__ void __launch_bounds__(GN_THREADS, GN_STATS_MINB) gn_stats_kernel(const bf16* __restrict__ x, int x_ld, int HW, int C, int G,
+                                                             int ppb, int nslab, int nitems,
+                                                             float* __restrict__ ws) {
   extern __shared__ float sh[];  // [rows][2][C]: per pixel-lane, per-channel sum | sumsq
-  const int b = blockIdx.y, split = blockIdx.x;
+  // PERSISTENT: one resident wave of blocks walks the (sample, slab) items round-robin.  A slab's partial sums are
+  // computed by the same threads in the same order whichever block owns it, so the statistics stay batch-invariant;
+  // the grid no longer quantises into waves (1216 blocks on 740 slots ran 1.64 waves at 2.9 TB/s).
+  for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+  const int b = item / nslab, split = item - b * nslab;
   const int vpr = C >> 3;  // 16-byte vectors per pixel row
   const int p0 = split * ppb;
   const int p1 = min(HW, p0 + ppb);
   const bf16* xb = x + (size_t)b * HW * x_ld;
-  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;   // threads across the channel dimension
+  const int lanes = gn_lanes(vpr);                         // threads across the channel dimension
   const int rows = GN_THREADS / lanes;                     // pixel rows processed in parallel
   const int prow = threadIdx.x / lanes;
   if (prow < rows) {
@@ -44,11 +66,22 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
       float s[8], q[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
-      int pp = p0 + prow;
-      for (; pp + 3 * rows < p1; pp += 4 * rows) {
-        uint4 u[4];
+      // Software pipeline, two rounds of four 16-byte loads: round r+1 is in flight while round r is summed (a
+      // load-4 / wait / sum-4 loop kept a warp without outstanding loads half of the time: 2.9 TB/s, 72 % of the
+      // samples on long_scoreboard).  80 registers = 3 blocks per SM; a rolling 4-slot refill capped at 64
+      // registers / 4 blocks measured slower.  Rounds past the end load zeros (predicated), so there is no serial
+      // tail and the order of the additions is the pixel order, as before.
+      const int n = (p1 - p0 - prow + rows - 1) / rows;  // pixels of this thread
+      const bf16* xv = xb + (size_t)(p0 + prow) * x_ld + v * 8;
+      const size_t pstride = (size_t)rows * x_ld;
+      auto ld = [&](uint4(&u)[4], int r) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) u[k] = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)(pp + k * rows) * x_ld) + v);
+        for (int k = 0; k < 4; ++k) {
+          const int jx = r * 4 + k;
+          u[k] = jx < n ? __ldg(reinterpret_cast<const uint4*>(xv + jx * pstride)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      };
+      auto acc = [&](const uint4(&u)[4]) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float f[8];
@@ -59,15 +92,15 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
             q[i] = fmaf(f[i], f[i], q[i]);
           }
         }
-      }
-      for (; pp < p1; pp += rows) {
-        float f[8];
-        unpack8(__ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v), f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          s[i] += f[i];
-          q[i] = fmaf(f[i], f[i], q[i]);
-        }
+      };
+      const int R = (n + 3) >> 2;
+      uint4 ua[4], ub[4];
+      if (R > 0) ld(ua, 0);
+      for (int r = 0; r < R; r += 2) {
+        if (r + 1 < R) ld(ub, r + 1);
+        acc(ua);
+        if (r + 2 < R) ld(ua, r + 2);
+        if (r + 1 < R) acc(ub);
       }
       *reinterpret_cast<float4*>(my_sum + v * 8) = make_float4(s[0], s[1], s[2], s[3]);
       *reinterpret_cast<float4*>(my_sum + v * 8 + 4) = make_float4(s[4], s[5], s[6], s[7]);
@@ -95,14 +128,16 @@ __global__ void __launch_bounds__(GN_THREADS) gn_stats_kernel(const bf16* __rest
     q += __shfl_xor_sync(0xffffffffu, q, o);
   }
   if (g < G && j == 0) {
-    float* o = ws + (((size_t)b * gridDim.x + split) * G + g) * 2;
+    float* o = ws + (((size_t)b * nslab + split) * G + g) * 2;
     o[0] = s;
     o[1] = q;
+  }
+  __syncthreads();  // the smem slots are rewritten by the next item
   }
 }
 
 // grid (splits2, B)
-__global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+__global__ void __launch_bounds__(GN_THREADS, GN_APPLY_MINB) gn_apply_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
                                                              int y_ld, int HW, int C, int G, int ppb, int nsplit_stats,
                                                              const float* __restrict__ ws,
                                                              const float* __restrict__ gamma,
@@ -149,44 +184,67 @@ __global__ void __launch_bounds__(GN_THREADS) gn_apply_kernel(const bf16* __rest
   const int p1 = min(HW, p0 + ppb);
   const bf16* xb = x + (size_t)b * HW * x_ld;
   bf16* yb = y + (size_t)b * HW * y_ld;
-  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;
+  const int lanes = gn_lanes(vpr);
   const int rows = GN_THREADS / lanes;
   const int prow = threadIdx.x / lanes;
   if (prow >= rows) return;
   for (int v = threadIdx.x % lanes; v < vpr; v += lanes) {
-    float a[8], c[8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      a[i] = sc[v * 8 + i];
-      c[i] = sf[v * 8 + i];
-    }
-    auto emit = [&](const uint4& u, int pp) {
+    // scale/shift are re-read from smem per vector (4 LDS.128 per 16-byte global load) instead of living in 16
+    // registers: the registers pay for a second round of loads in flight
+    const float4* sc4 = reinterpret_cast<const float4*>(sc + v * 8);
+    const float4* sf4 = reinterpret_cast<const float4*>(sf + v * 8);
+    auto emit = [&](const uint4& u, bf16* dst) {
       float f[8];
       unpack8(u, f);
+      {
+        const float4 a0 = sc4[0], a1 = sc4[1], c0 = sf4[0], c1 = sf4[1];
+        f[0] = fmaf(f[0], a0.x, c0.x); f[1] = fmaf(f[1], a0.y, c0.y); f[2] = fmaf(f[2], a0.z, c0.z); f[3] = fmaf(f[3], a0.w, c0.w);
+        f[4] = fmaf(f[4], a1.x, c1.x); f[5] = fmaf(f[5], a1.y, c1.y); f[6] = fmaf(f[6], a1.z, c1.z); f[7] = fmaf(f[7], a1.w, c1.w);
+      }
+      if (apply_silu) {
+        // t / (1 + 2^(-t log2 e)), ONE MUFU.RCP per pair of elements: 1/d0 = d1 / (d0 d1).  The exponent is clamped
+        // at 63 so the product stays finite (t < -43.7 gives t * 2^-63 instead of t * e^t: both are 0 in bf16).
+        // At the HBM roofline the two-MUFU form would keep the 16/clk XU pipe 80 % busy; this one 60 %.
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float t = fmaf(f[i], a[i], c[i]);
-        f[i] = apply_silu ? __fdividef(t, 1.0f + __expf(-t)) : t;
+        for (int i = 0; i < 8; i += 2) {
+          const float d0 = 1.0f + fast_exp2(fminf(f[i] * -1.4426950408889634f, 63.0f));
+          const float d1 = 1.0f + fast_exp2(fminf(f[i + 1] * -1.4426950408889634f, 63.0f));
+          float r;
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d0 * d1));
+          f[i] *= r * d1;
+          f[i + 1] *= r * d0;
+        }
       }
       uint4 o;
       o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
       o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-      *(reinterpret_cast<uint4*>(yb + (size_t)pp * y_ld) + v) = o;
+      *reinterpret_cast<uint4*>(dst) = o;
     };
-    int pp = p0 + prow;
-    for (; pp + 3 * rows < p1; pp += 4 * rows) {
+    // (a two-round software pipeline like the statistics pass costs 16 registers = one resident block: measured slower)
+    const int n = (p1 - p0 - prow + rows - 1) / rows;
+    const bf16* xv = xb + (size_t)(p0 + prow) * x_ld + v * 8;
+    bf16* yv = yb + (size_t)(p0 + prow) * y_ld + v * 8;
+    const size_t xs = (size_t)rows * x_ld, ys = (size_t)rows * y_ld;
+    for (int r = 0; r * 4 < n; ++r) {
       uint4 u[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) u[k] = __ldg(reinterpret_cast<const uint4*>(xb + (size_t)(pp + k * rows) * x_ld) + v);
+      for (int k = 0; k < 4; ++k) {
+        const int jx = r * 4 + k;
+        u[k] = jx < n ? __ldg(reinterpret_cast<const uint4*>(xv + jx * xs)) : make_uint4(0u, 0u, 0u, 0u);
+      }
 #pragma unroll
-      for (int k = 0; k < 4; ++k) emit(u[k], pp + k * rows);
+      for (int k = 0; k < 4; ++k) {
+        const int jx = r * 4 + k;
+        if (jx < n) emit(u[k], yv + jx * ys);
+      }
     }
-    for (; pp < p1; pp += rows) emit(__ldg(reinterpret_cast<const uint4*>(xb + (size_t)pp * x_ld) + v), pp);
   }
 }
 
-static int gn_splits(int B, int HW) {
-  int s = (4 * 148 + B - 1) / B;  // ~4 CTAs per SM across the batch
+// Slabs per sample of the apply pass: the whole grid must be resident at once.  (Rounding UP to "about 4 CTAs per
+// SM" put 16 of the 608 blocks of the 64x64x320 level into a second wave that ran alone, latency bound.)
+static int gn_splits(int B, int HW, int blocks_per_sm) {
+  int s = (148 * blocks_per_sm) / B;
   if (s > GN_MAX_SPLITS) s = GN_MAX_SPLITS;
   if (s > HW) s = HW;
   if (s < 1) s = 1;
@@ -195,11 +253,18 @@ static int gn_splits(int B, int HW) {
 
 // pixels per statistics slab: a function of (HW, C) ONLY (never of the batch), ~80 KB of activations per block
 static int gn_stats_ppb(int HW, int C) {
+  static const int slab_bytes = [] { const char* e = getenv("TOPO_GN_SLAB_KB"); return (e ? atoi(e) : 80) * 1024; }();
   int ppb = 16;
-  while (ppb * 2 * C * 2 <= 81920) ppb *= 2;
+  while (ppb * 2 * C * 2 <= slab_bytes) ppb *= 2;
   // at most 64 slabs per sample: short-lived 256 KB blocks cost the 512x512 VAE levels 20 % (measured)
-  const int min_ppb = (HW + 63) / 64;
+  static const int max_slabs = [] { const char* e = getenv("TOPO_GN_MAX_SLABS"); return e ? atoi(e) : 64; }();
+  const int min_ppb = (HW + max_slabs - 1) / max_slabs;
   if (ppb < min_ppb) ppb = min_ppb;
+  // small levels (8x8, 16x16): at least 16 slabs per sample as long as every thread keeps one 4-deep round of loads
+  // (a 256-pixel sample walked by 160 threads in 8 dependent rounds was latency bound)
+  const int rows = GN_THREADS / gn_lanes(C / 8);
+  const int cap = (4 * rows > HW / 16) ? 4 * rows : HW / 16;
+  if (ppb > cap) ppb = cap;
   if (ppb > HW) ppb = HW;
   return ppb;
 }
@@ -215,7 +280,7 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
   const int ppb_s = gn_stats_ppb(HW, C);
   const int nsplit_s = (HW + ppb_s - 1) / ppb_s;
   const int vpr = C / 8;
-  const int lanes = vpr < GN_THREADS ? vpr : GN_THREADS;
+  const int lanes = gn_lanes(vpr);
   const int rows = GN_THREADS / lanes;
   const size_t smem_s = (size_t)rows * 2 * C * sizeof(float);
   static size_t smem_set = 48 * 1024;
@@ -223,11 +288,19 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
     TOPO_CUDA(cudaFuncSetAttribute(gn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
     smem_set = smem_s;
   }
-  gn_stats_kernel<<<dim3(nsplit_s, B), GN_THREADS, smem_s, st>>>(reinterpret_cast<const bf16*>(x), x_ld, HW, C, G, ppb_s, ws);
-  const int splits = gn_splits(B, HW);
+  int bps_s = 0;
+  TOPO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, gn_stats_kernel, GN_THREADS, smem_s));
+  const int nitems = nsplit_s * B;
+  const int grid_s = nitems < 148 * bps_s ? nitems : 148 * (bps_s > 0 ? bps_s : 1);
+  gn_stats_kernel<<<grid_s, GN_THREADS, smem_s, st>>>(reinterpret_cast<const bf16*>(x), x_ld, HW, C, G, ppb_s, nsplit_s,
+                                                      nitems, ws);
+  const int smem_a = (2 * C + 2 * G) * (int)sizeof(float);
+  int bps = 0;
+  TOPO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, gn_apply_kernel, GN_THREADS, smem_a));
+  const int splits = gn_splits(B, HW, bps > 0 ? bps : 1);
   const int ppb = (HW + splits - 1) / splits;
   const int nsplit = (HW + ppb - 1) / ppb;
-  gn_apply_kernel<<<dim3(nsplit, B), GN_THREADS, (2 * C + 2 * G) * sizeof(float), st>>>(
+  gn_apply_kernel<<<dim3(nsplit, B), GN_THREADS, smem_a, st>>>(
       reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), y_ld, HW, C, G, ppb, nsplit_s, ws, gamma, beta,
       eps, apply_silu);
   TOPO_CUDA(cudaGetLastError());
