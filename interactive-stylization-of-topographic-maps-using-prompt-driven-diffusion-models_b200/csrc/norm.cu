@@ -13,6 +13,9 @@ namespace topo {
 constexpr int GN_THREADS = 256;
 constexpr int GN_MAX_SPLITS = 256;
 constexpr int GN_MAX_C = 4096;
+#ifndef LN_MINB
+#define LN_MINB 2
+#endif
 #ifndef GN_STATS_MINB
 #define GN_STATS_MINB 3
 #endif
@@ -374,56 +377,75 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const bf16* __restrict__
 // warp has 32 * V independent 16-byte loads in flight (C = 320: four rows per warp instead of one row on 40 of 64 lane
 // slots).  Same exact two-pass variance, reductions over the G-lane group only.
 template <int G, int V>
-__global__ void __launch_bounds__(256) layernorm_group_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+__global__ void __launch_bounds__(256, LN_MINB) layernorm_group_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
                                                              int y_ld, int M, const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, float eps) {
   constexpr int C = G * V * 8;
   constexpr int RPW = 32 / G;
   const int lane = threadIdx.x & 31;
   const int l = lane % G;
-  const int row = (blockIdx.x * 8 + (threadIdx.x >> 5)) * RPW + lane / G;
-  const bool ok = row < M;
-  const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)(ok ? row : 0) * x_ld);
-  float f[V][8];
-  float s = 0.f;
+  // PERSISTENT with a one-row-group prefetch: the raw 16-byte vectors of the next row group are in flight while
+  // this one is reduced, normalised and stored (blocks that load once, wait, compute and exit ran at 55 % of the
+  // copy bandwidth).
+  const int nblk = (M + 8 * RPW - 1) / (8 * RPW);
+  auto row_of = [&](int blk) { return (blk * 8 + (int)(threadIdx.x >> 5)) * RPW + lane / G; };
+  uint4 u[V];
+  {
+    const int row = row_of(blockIdx.x);
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (size_t)(row < M ? row : 0) * x_ld);
 #pragma unroll
-  for (int k = 0; k < V; ++k) {
-    unpack8(__ldg(xr + l + k * G), f[k]);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s += f[k][i];
+    for (int k = 0; k < V; ++k) u[k] = __ldg(xr + l + k * G);
   }
+  for (int blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+    const int row = row_of(blk);
+    const bool ok = row < M;
+    float f[V][8];
+    float s = 0.f;
 #pragma unroll
-  for (int o = G / 2; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  const float mean = s * (1.0f / C);
-  float q = 0.f;
+    for (int k = 0; k < V; ++k) {
+      unpack8(u[k], f[k]);
 #pragma unroll
-  for (int k = 0; k < V; ++k)
+      for (int i = 0; i < 8; ++i) s += f[k][i];
+    }
+    if (blk + (int)gridDim.x < nblk) {
+      const int rn = row_of(blk + gridDim.x);
+      const uint4* xn = reinterpret_cast<const uint4*>(x + (size_t)(rn < M ? rn : 0) * x_ld);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float d = f[k][i] - mean;
-      q = fmaf(d, d, q);
+      for (int k = 0; k < V; ++k) u[k] = __ldg(xn + l + k * G);
     }
 #pragma unroll
-  for (int o = G / 2; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-  const float rstd = rsqrtf(q * (1.0f / C) + eps);
-  if (!ok) return;
-  uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * y_ld);
+    for (int o = G / 2; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s * (1.0f / C);
+    float q = 0.f;
 #pragma unroll
-  for (int k = 0; k < V; ++k) {
-    const int v = l + k * G;
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v);
-    const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v + 1);
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v);
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v + 1);
-    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-    float r[8];
+    for (int k = 0; k < V; ++k)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r[i] = fmaf((f[k][i] - mean) * rstd, gg[i], bb[i]);
-    uint4 o;
-    o.x = pack_bf16x2(r[0], r[1]); o.y = pack_bf16x2(r[2], r[3]);
-    o.z = pack_bf16x2(r[4], r[5]); o.w = pack_bf16x2(r[6], r[7]);
-    yr[v] = o;
+      for (int i = 0; i < 8; ++i) {
+        const float d = f[k][i] - mean;
+        q = fmaf(d, d, q);
+      }
+#pragma unroll
+    for (int o = G / 2; o; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+    const float rstd = rsqrtf(q * (1.0f / C) + eps);
+    if (!ok) continue;
+    uint4* yr = reinterpret_cast<uint4*>(y + (size_t)row * y_ld);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const int v = l + k * G;
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v);
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + 2 * v + 1);
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v);
+      const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta) + 2 * v + 1);
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      float r[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) r[i] = fmaf((f[k][i] - mean) * rstd, gg[i], bb[i]);
+      uint4 o;
+      o.x = pack_bf16x2(r[0], r[1]); o.y = pack_bf16x2(r[2], r[3]);
+      o.z = pack_bf16x2(r[4], r[5]); o.w = pack_bf16x2(r[6], r[7]);
+      yr[v] = o;
+    }
   }
 }
 
@@ -431,7 +453,15 @@ template <int G, int V>
 static void launch_ln_group(const bf16* x, int x_ld, bf16* y, int y_ld, int M, const float* gamma, const float* beta,
                             float eps, cudaStream_t st) {
   const int rows_per_block = 8 * (32 / G);
-  layernorm_group_kernel<G, V><<<(M + rows_per_block - 1) / rows_per_block, 256, 0, st>>>(x, x_ld, y, y_ld, M, gamma, beta, eps);
+  const int nblk = (M + rows_per_block - 1) / rows_per_block;
+  static int bps = 0;  // per instantiation
+  if (bps == 0) {
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, layernorm_group_kernel<G, V>, 256, 0);
+    if (bps < 1) bps = 1;
+  }
+  static const bool persistent = [] { const char* e = getenv("TOPO_LN_PERSIST"); return !e || atoi(e) != 0; }();
+  const int grid = (persistent && nblk > 148 * bps) ? 148 * bps : nblk;
+  layernorm_group_kernel<G, V><<<grid, 256, 0, st>>>(x, x_ld, y, y_ld, M, gamma, beta, eps);
 }
 
 int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int M, int C,
