@@ -473,15 +473,37 @@ def run_first_block_shared(layers, h_full: torch.Tensor, Bs: int, rep: int, H: i
     h = gemm(gn(r, Bs, st.norm, False), st.proj_in)
     b0 = st.blocks[0]
     h = run_attn(b0.attn1, ln(h, b0.n1), h, Bs, None)
-    h, r = h.repeat(rep, 1), r.repeat(rep, 1)
-    _count(2)
     Be = Bs * rep
-    h = run_attn(b0.attn2, ln(h, b0.n2), h, Be, kvs[0])
+    a2 = b0.attn2
+    if getattr(a2.module, "control_states", None) is None:
+        # The context enters through K/V only: LayerNorm and the q projection of the first CROSS-attention are shared
+        # too, and the copies differ from here on.  Nothing is repeated in memory: the attention and its out-projection
+        # run once per copy on the shared q / shared residual and write their slice of the full-batch tensors.
+        N, hdp = H * W, a2.hdp
+        q = gemm(ln(h, b0.n2), a2.q).view(Bs, N, hdp)
+        k, v = kvs[0]
+        Nk = k.shape[1]
+        o = torch.empty(Be, N, hdp, dtype=BF16, device=h.device)
+        hf = torch.empty(Be * N, h.shape[1], dtype=BF16, device=h.device)
+        for i in range(rep):
+            sl = slice(i * Bs, (i + 1) * Bs)
+            _rec("attn_cross", 4.0 * Bs * a2.heads * N * Nk * a2.d, 2.0 * (2 * M * hdp + 2 * Bs * Nk * hdp),
+                 lambda: ops.attention(q, k[sl], v[sl], a2.heads, a2.dp, a2.scale, out=o[sl]), f"B{Bs} N{N} Nk{Nk} d{a2.d}")
+            _count()
+            gemm(o[sl].view(M, hdp), a2.o, out=hf[i * M:(i + 1) * M], res=h)
+        h = hf
+    else:
+        h = h.repeat(rep, 1)
+        _count()
+        h = run_attn(a2, ln(h, b0.n2), h, Be, kvs[0])
     g = gemm(ln(h, b0.n3), b0.ff0, act=ACT_GEGLU)
     h = gemm(g, b0.ff2, res=h)
     for blk, kv in zip(st.blocks[1:], kvs[1:]):
         h = run_block(blk, h, Be, kv)
-    return gemm(h, st.proj_out, res=r)
+    out = torch.empty(Be * H * W, st.proj_out.N, dtype=BF16, device=h.device)
+    for i in range(rep):  # the block's residual r is shared as well: one GEMM per copy instead of r.repeat
+        gemm(h[i * M:(i + 1) * M], st.proj_out, out=out[i * M:(i + 1) * M], res=r)
+    return out
 
 
 def _block_out_channels(layers) -> int:

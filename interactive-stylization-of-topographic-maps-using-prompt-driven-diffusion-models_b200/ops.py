@@ -165,13 +165,15 @@ def conv3x3(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = Non
 
 
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp: int, scale: float,
-              kv_len: Optional[torch.Tensor] = None) -> torch.Tensor:
+              kv_len: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """q [B,Nq,heads*dp], k/v [B,Nk,heads*dp] (bf16, padded head columns zero) -> o [B,Nq,heads*dp].
     ``kv_len`` (int32 [B] on the device): keys at or beyond the sample's length are masked (right-padded prompts)."""
     _cuda(q, "attention")
     Bn, Nq, ld = q.shape
     Nk = k.shape[1]
-    o = torch.empty(Bn, Nq, heads * dp, dtype=BF16, device=q.device)
+    o = torch.empty(Bn, Nq, heads * dp, dtype=BF16, device=q.device) if out is None else out
+    if o.shape != (Bn, Nq, heads * dp) or o.dtype != BF16 or not o.is_contiguous():
+        raise capi.TopoError(f"attention: out must be a contiguous bf16 [{Bn},{Nq},{heads * dp}] tensor")
     if kv_len is not None:
         kv_len = kv_len.to(device=q.device, dtype=torch.int32).contiguous()
         capi.check(capi.load_library().topo_attention_varlen(
