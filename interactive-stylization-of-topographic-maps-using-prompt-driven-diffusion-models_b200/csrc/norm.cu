@@ -139,6 +139,35 @@ __global__ void __launch_bounds__(GN_THREADS, GN_STATS_MINB) gn_stats_kernel(con
   }
 }
 
+// y = silu?(x * scale + shift) on one 16-byte vector; scale/shift read from smem (4 LDS.128)
+__device__ __forceinline__ void gn_emit(const uint4& u, const float4* sc4, const float4* sf4, int apply_silu, bf16* dst) {
+  float f[8];
+  unpack8(u, f);
+  {
+    const float4 a0 = sc4[0], a1 = sc4[1], c0 = sf4[0], c1 = sf4[1];
+    f[0] = fmaf(f[0], a0.x, c0.x); f[1] = fmaf(f[1], a0.y, c0.y); f[2] = fmaf(f[2], a0.z, c0.z); f[3] = fmaf(f[3], a0.w, c0.w);
+    f[4] = fmaf(f[4], a1.x, c1.x); f[5] = fmaf(f[5], a1.y, c1.y); f[6] = fmaf(f[6], a1.z, c1.z); f[7] = fmaf(f[7], a1.w, c1.w);
+  }
+  if (apply_silu) {
+    // t / (1 + 2^(-t log2 e)), ONE MUFU.RCP per pair of elements: 1/d0 = d1 / (d0 d1).  The exponent is clamped
+    // at 63 so the product stays finite (t < -43.7 gives t * 2^-63 instead of t * e^t: both are 0 in bf16).
+    // At the HBM roofline the two-MUFU form would keep the 16/clk XU pipe 80 % busy; this one 60 %.
+#pragma unroll
+    for (int i = 0; i < 8; i += 2) {
+      const float d0 = 1.0f + fast_exp2(fminf(f[i] * -1.4426950408889634f, 63.0f));
+      const float d1 = 1.0f + fast_exp2(fminf(f[i + 1] * -1.4426950408889634f, 63.0f));
+      float r;
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d0 * d1));
+      f[i] *= r * d1;
+      f[i + 1] *= r * d0;
+    }
+  }
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+  *reinterpret_cast<uint4*>(dst) = o;
+}
+
 // grid (splits2, B)
 __global__ void __launch_bounds__(GN_THREADS, GN_APPLY_MINB) gn_apply_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
                                                              int y_ld, int HW, int C, int G, int ppb, int nsplit_stats,
@@ -196,33 +225,7 @@ __global__ void __launch_bounds__(GN_THREADS, GN_APPLY_MINB) gn_apply_kernel(con
     // registers: the registers pay for a second round of loads in flight
     const float4* sc4 = reinterpret_cast<const float4*>(sc + v * 8);
     const float4* sf4 = reinterpret_cast<const float4*>(sf + v * 8);
-    auto emit = [&](const uint4& u, bf16* dst) {
-      float f[8];
-      unpack8(u, f);
-      {
-        const float4 a0 = sc4[0], a1 = sc4[1], c0 = sf4[0], c1 = sf4[1];
-        f[0] = fmaf(f[0], a0.x, c0.x); f[1] = fmaf(f[1], a0.y, c0.y); f[2] = fmaf(f[2], a0.z, c0.z); f[3] = fmaf(f[3], a0.w, c0.w);
-        f[4] = fmaf(f[4], a1.x, c1.x); f[5] = fmaf(f[5], a1.y, c1.y); f[6] = fmaf(f[6], a1.z, c1.z); f[7] = fmaf(f[7], a1.w, c1.w);
-      }
-      if (apply_silu) {
-        // t / (1 + 2^(-t log2 e)), ONE MUFU.RCP per pair of elements: 1/d0 = d1 / (d0 d1).  The exponent is clamped
-        // at 63 so the product stays finite (t < -43.7 gives t * 2^-63 instead of t * e^t: both are 0 in bf16).
-        // At the HBM roofline the two-MUFU form would keep the 16/clk XU pipe 80 % busy; this one 60 %.
-#pragma unroll
-        for (int i = 0; i < 8; i += 2) {
-          const float d0 = 1.0f + fast_exp2(fminf(f[i] * -1.4426950408889634f, 63.0f));
-          const float d1 = 1.0f + fast_exp2(fminf(f[i + 1] * -1.4426950408889634f, 63.0f));
-          float r;
-          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d0 * d1));
-          f[i] *= r * d1;
-          f[i + 1] *= r * d0;
-        }
-      }
-      uint4 o;
-      o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-      o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-      *reinterpret_cast<uint4*>(dst) = o;
-    };
+    auto emit = [&](const uint4& u, bf16* dst) { gn_emit(u, sc4, sf4, apply_silu, dst); };
     // (a two-round software pipeline like the statistics pass costs 16 registers = one resident block: measured slower)
     const int n = (p1 - p0 - prow + rows - 1) / rows;
     const bf16* xv = xb + (size_t)(p0 + prow) * x_ld + v * 8;
@@ -272,6 +275,127 @@ static int gn_stats_ppb(int HW, int C) {
   return ppb;
 }
 
+// Small levels (16x16, 8x8): ONE kernel.  A CTA owns `chunk` channels (whole groups, a multiple of 8) of one sample and
+// keeps its slice of the activation in REGISTERS (at most MAXV 16-byte vectors per thread): load once, per-channel
+// sums -> smem fold per group -> scale/shift -> normalise from the registers -> store.  One read, one write, no
+// workspace round trip and one launch instead of two (the pair cost 24-31 us on 6-25 MB tensors).  Per-sample and
+// fixed-order, hence deterministic and batch-invariant like the two-pass path.
+template <int MAXV>
+__global__ void __launch_bounds__(GN_THREADS) gn_small_kernel(const bf16* __restrict__ x, int x_ld, bf16* __restrict__ y,
+                                                             int y_ld, int HW, int C, int G, int chunk,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps, int apply_silu) {
+  extern __shared__ float sh[];  // [rows][2][chunk] sums | scale[chunk] | shift[chunk] | mean,rstd[2 * gpc] | [parts][2][chunk]
+  const int b = blockIdx.y, c0 = blockIdx.x * chunk;
+  const int vpc = chunk >> 3, rows = GN_THREADS / vpc;
+  const int prow = threadIdx.x / vpc, cv = threadIdx.x - prow * vpc;
+  const int cpg = C / G, gpc = chunk / cpg;
+  float* sc = sh + (size_t)rows * 2 * chunk;
+  float* sf = sc + chunk;
+  float* mr = sf + chunk;
+  const int n = prow < rows ? (HW - prow + rows - 1) / rows : 0;
+  const bf16* xv = x + ((size_t)b * HW + prow) * x_ld + c0 + cv * 8;
+  const size_t xs = (size_t)rows * x_ld;
+  uint4 u[MAXV];
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j)
+    u[j] = j < n ? __ldg(reinterpret_cast<const uint4*>(xv + j * xs)) : make_uint4(0u, 0u, 0u, 0u);
+  if (prow < rows) {
+    float s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXV; ++j) {
+      float f[8];
+      unpack8(u[j], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s[i] += f[i];
+        q[i] = fmaf(f[i], f[i], q[i]);
+      }
+    }
+    float* my = sh + (size_t)prow * 2 * chunk + cv * 8;
+    *reinterpret_cast<float4*>(my) = make_float4(s[0], s[1], s[2], s[3]);
+    *reinterpret_cast<float4*>(my + 4) = make_float4(s[4], s[5], s[6], s[7]);
+    *reinterpret_cast<float4*>(my + chunk) = make_float4(q[0], q[1], q[2], q[3]);
+    *reinterpret_cast<float4*>(my + chunk + 4) = make_float4(q[4], q[5], q[6], q[7]);
+  }
+  __syncthreads();
+  // Fold in two fixed-order stages that use the whole block (8 threads per group walking up to 51 pixel rows was a
+  // 500-load dependent chain): (1) thread (part, channel) sums the rows part, part + parts, ...; (2) one warp per
+  // group sums the parts x cpg entries, lane l taking entries l, l + 32, ..., then a shuffle tree.
+  const int parts = GN_THREADS / chunk;
+  float* pp = mr + 2 * gpc;  // [parts][2][chunk]
+  if ((int)threadIdx.x < parts * chunk) {
+    const int part = threadIdx.x / chunk, ch = threadIdx.x - part * chunk;
+    float s = 0.f, q = 0.f;
+    for (int r = part; r < rows; r += parts) {
+      s += sh[(size_t)r * 2 * chunk + ch];
+      q += sh[(size_t)r * 2 * chunk + chunk + ch];
+    }
+    pp[(size_t)part * 2 * chunk + ch] = s;
+    pp[(size_t)part * 2 * chunk + chunk + ch] = q;
+  }
+  __syncthreads();
+  {
+    const int g = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (g < gpc) {  // warp-uniform
+      float s = 0.f, q = 0.f;
+      for (int e = l; e < parts * cpg; e += 32) {
+        const int part = e / cpg, i = e - part * cpg;
+        s += pp[(size_t)part * 2 * chunk + g * cpg + i];
+        q += pp[(size_t)part * 2 * chunk + chunk + g * cpg + i];
+      }
+#pragma unroll
+      for (int o = 16; o; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+      }
+      if (l == 0) {
+        const float nn = (float)HW * cpg;
+        const float mean = s / nn;
+        const float var = fmaxf(q / nn - mean * mean, 0.f);
+        mr[2 * g] = mean;
+        mr[2 * g + 1] = rsqrtf(var + eps);
+      }
+    }
+  }
+  __syncthreads();
+  for (int ch = threadIdx.x; ch < chunk; ch += GN_THREADS) {
+    const int g = ch / cpg;
+    const float a = gamma[c0 + ch] * mr[2 * g + 1];
+    sc[ch] = a;
+    sf[ch] = beta[c0 + ch] - mr[2 * g] * a;
+  }
+  __syncthreads();
+  if (prow >= rows) return;
+  const float4* sc4 = reinterpret_cast<const float4*>(sc + cv * 8);
+  const float4* sf4 = reinterpret_cast<const float4*>(sf + cv * 8);
+  bf16* yv = y + ((size_t)b * HW + prow) * y_ld + c0 + cv * 8;
+  const size_t ys = (size_t)rows * y_ld;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j)
+    if (j < n) gn_emit(u[j], sc4, sf4, apply_silu, yv + j * ys);
+}
+
+// chunk (channels per CTA) of the fused small-level kernel, 0 = not applicable
+static int gn_small_chunk(int HW, int C, int G, int* maxv) {
+  static const bool on = [] { const char* e = getenv("TOPO_GN_FUSED_SMALL"); return !e || atoi(e) != 0; }();
+  if (!on || HW > 256) return 0;
+  const int cpg = C / G;
+  int unit = cpg;
+  while (unit % 8) unit += cpg;  // lcm(cpg, 8): whole groups and whole 16-byte vectors
+  if (unit > 128 || C % unit) return 0;
+  int chunk = unit;
+  while (HW * chunk * 2 < 16384 && C % (chunk * 2) == 0 && chunk * 2 <= 256) chunk *= 2;
+  if (chunk / cpg * 32 > GN_THREADS) return 0;  // one warp per group in the fold
+  const int rows = GN_THREADS / (chunk / 8);
+  const int n = (HW + rows - 1) / rows;
+  if (n > 16) return 0;
+  *maxv = n <= 8 ? 8 : 16;
+  return chunk;
+}
+
 int groupnorm_ws_floats(int B, int G) { return B * G * 2 * GN_MAX_SPLITS; }
 
 int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int B, int HW,
@@ -280,6 +404,20 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
   TOPO_CHECK(G * 8 <= GN_THREADS, TOPO_E_INVAL, "groupnorm: at most %d groups", GN_THREADS / 8);
   TOPO_CHECK(x_ld % 8 == 0 && y_ld % 8 == 0, TOPO_E_INVAL, "groupnorm: leading dims must be multiples of 8");
   TOPO_CHECK(ws != nullptr, TOPO_E_INVAL, "groupnorm: workspace required");
+  int maxv = 0;
+  if (const int chunk = gn_small_chunk(HW, C, G, &maxv)) {
+    const int rows = GN_THREADS / (chunk / 8);
+    const size_t smem = ((size_t)rows * 2 * chunk + 2 * chunk + 2 * (chunk / (C / G)) + (GN_THREADS / chunk) * 2 * chunk) * sizeof(float);
+    const dim3 grid(C / chunk, B);
+    if (maxv == 8)
+      gn_small_kernel<8><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y),
+                                                          y_ld, HW, C, G, chunk, gamma, beta, eps, apply_silu);
+    else
+      gn_small_kernel<16><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y),
+                                                           y_ld, HW, C, G, chunk, gamma, beta, eps, apply_silu);
+    TOPO_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int ppb_s = gn_stats_ppb(HW, C);
   const int nsplit_s = (HW + ppb_s - 1) / ppb_s;
   const int vpr = C / 8;

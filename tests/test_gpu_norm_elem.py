@@ -12,7 +12,11 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("B,HW,C,silu,eps", [(2, 4096, 320, True, 1e-5), (2, 1024, 1920, True, 1e-5),
                                              (3, 64, 2560, True, 1e-5), (2, 256, 1280, False, 1e-6),
-                                             (1, 16384, 128, True, 1e-6), (2, 1024, 960, True, 1e-5)])
+                                             (1, 16384, 128, True, 1e-6), (2, 1024, 960, True, 1e-5),
+                                             # the fused one-kernel path of the 16x16 / 8x8 levels (register-resident slices)
+                                             (3, 64, 1280, True, 1e-5), (2, 256, 640, True, 1e-5),
+                                             (2, 256, 1920, True, 1e-5), (2, 256, 2560, True, 1e-5),
+                                             (5, 256, 320, False, 1e-5), (2, 100, 1280, True, 1e-5)])
 def test_groupnorm_silu(B, HW, C, silu, eps):
     from topo_b200 import ops
     x = (rnd(B, HW, C, seed=1) * 1.5 + 0.3).to(BF16)
