@@ -125,6 +125,9 @@ int topo_timestep_embedding(topo_handle_t h, const float* t, void* emb, int B, i
  *   eps holds [uncond ; cond] (2n values) when cfg != 0, else n values.  All fp32.                    */
 int topo_ddim_step(topo_handle_t h, const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w,
                    float a_t, float a_prev, float sigma, const float* noise, void* stream);
+/* same, also writing pred_x0 = x0 (the `intermediates["pred_x0"]` list of ldm's DDIMSampler.sample)   */
+int topo_ddim_step_x0(topo_handle_t h, const float* x, const float* eps, float* x_out, float* pred_x0, int64_t n, int cfg,
+                      float w, float a_t, float a_prev, float sigma, const float* noise, void* stream);
 /* direct convolution for the narrow layers (C_in not a multiple of 64: conv_in, the hint block, VAE conv_in):
  *   x NHWC [B,H,W,Cin] bf16, w bf16 [Cout, kh*kw*Cin], out NHWC [B,Ho,Wo,Cout]; optional SiLU; out += add if add.
  *   pad_lo = zero rows/columns before the image (-1: ksize/2, the symmetric convolution).  pad_lo = 0 with ksize 3,

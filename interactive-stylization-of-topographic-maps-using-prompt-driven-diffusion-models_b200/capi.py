@@ -21,7 +21,7 @@ ACT_NONE, ACT_SILU, ACT_GEGLU, ACT_GELU, ACT_RELU = 0, 1, 2, 3, 4
 SYMBOLS = [
     "topo_create", "topo_destroy", "topo_last_error", "topo_version", "topo_lora_linear", "topo_conv3x3",
     "topo_attention", "topo_attention_varlen", "topo_embed_sum", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
-    "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_conv_direct",
+    "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_ddim_step_x0", "topo_conv_direct",
     "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_tile_metrics", "topo_im2col3x3_s1_k64",
     "topo_add_bf16", "topo_tile_to_u8", "topo_tile_to_u8_round", "topo_softmax_rows", "topo_geglu_tile",
 ]
@@ -74,6 +74,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_zeroconv_residual.argtypes = [vp, vp, i32, vp, vp, f32, vp, i32, vp, i32, i32, i32, i32, vp]
     lib.topo_timestep_embedding.argtypes = [vp, vp, vp, i32, i32, vp]
     lib.topo_ddim_step.argtypes = [vp, vp, vp, vp, i64, i32, f32, f32, f32, f32, vp, vp]
+    lib.topo_ddim_step_x0.argtypes = [vp, vp, vp, vp, vp, i64, i32, f32, f32, f32, f32, vp, vp]
     lib.topo_conv_direct.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp,
                                      i32, i32, vp]
     lib.topo_nchw_f32_to_nhwc_bf16.argtypes = [vp, vp, vp, i32, i32, i32, i32, vp]

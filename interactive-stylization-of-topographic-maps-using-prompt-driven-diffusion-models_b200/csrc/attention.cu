@@ -321,11 +321,7 @@ template <int DP, int NS, int NPOLY, bool EARLY = true>
 static int launch_attention(const AttnParams& p, int B, cudaStream_t st) {
   using L = AttnSmem<DP, NS, EARLY>;
   auto kfn = attention_kernel<DP, NS, NPOLY, EARLY>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    attr_set = true;
-  }
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
   dim3 grid((p.Nq + ATT_BM * NS - 1) / (ATT_BM * NS), p.heads, B);
   kfn<<<grid, L::THREADS, L::TOTAL, st>>>(p);
   TOPO_CUDA(cudaGetLastError());

@@ -4,6 +4,10 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 #include "topo_b200.h"
 
@@ -16,6 +20,31 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+int ensure_dyn_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, int> done;
+  int dev = 0;
+  TOPO_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  int& have = done[std::make_pair(dev, kernel)];
+  if (have >= bytes) return 0;
+  TOPO_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  have = bytes;
+  return 0;
+}
+
+int device_sm_count() {
+  static int cache[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!cache[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cache[dev] = n;
+  }
+  return cache[dev];
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -85,7 +114,7 @@ int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
                        float eps, cudaStream_t st);
 int timestep_embedding_dispatch(const float* t, void* emb, int B, int dim, cudaStream_t st);
 int ddim_step_dispatch(const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w, float a_t,
-                       float a_prev, float sigma, const float* noise, cudaStream_t st);
+                       float a_prev, float sigma, const float* noise, float* pred_x0, cudaStream_t st);
 int conv_direct_dispatch(const void* x, int x_ld, const void* w, const float* bias, void* out, int out_ld, int B, int H,
                          int W, int Cin, int Cout, int ksize, int stride, int pad_lo, int act, const void* add,
                          int add_ld, int out_fp32, cudaStream_t st);
@@ -253,7 +282,14 @@ int topo_timestep_embedding(topo_handle_t h, const float* t, void* emb, int B, i
 int topo_ddim_step(topo_handle_t h, const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w,
                    float a_t, float a_prev, float sigma, const float* noise, void* stream) {
   H_CHECK(h);
-  return ddim_step_dispatch(x, eps, x_out, n, cfg, w, a_t, a_prev, sigma, noise, ST(stream));
+  return ddim_step_dispatch(x, eps, x_out, n, cfg, w, a_t, a_prev, sigma, noise, nullptr, ST(stream));
+}
+
+int topo_ddim_step_x0(topo_handle_t h, const float* x, const float* eps, float* x_out, float* pred_x0, int64_t n, int cfg,
+                      float w, float a_t, float a_prev, float sigma, const float* noise, void* stream) {
+  H_CHECK(h);
+  TOPO_CHECK(x && eps && x_out && pred_x0, TOPO_E_INVAL, "topo_ddim_step_x0: null argument");
+  return ddim_step_dispatch(x, eps, x_out, n, cfg, w, a_t, a_prev, sigma, noise, pred_x0, ST(stream));
 }
 
 int topo_conv_direct(topo_handle_t h, const void* x, int x_ld, const void* w, const float* bias, void* out, int out_ld,

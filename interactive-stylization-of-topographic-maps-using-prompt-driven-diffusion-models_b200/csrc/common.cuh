@@ -37,6 +37,12 @@ void set_error(const char* fmt, ...);
 int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
               const uint32_t* box, int swizzle_bytes /*0,32,64,128*/);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a PER-DEVICE function attribute: remembered per (device, kernel) so that
+// one process driving several GPUs sets it on each of them (a process-wide `static bool` would skip the second GPU).
+int ensure_dyn_smem(const void* kernel, int bytes);
+// SM count of the CURRENT device (cached per device)
+int device_sm_count();
+
 // ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------

@@ -29,7 +29,8 @@ int timestep_embedding_dispatch(const float* t, void* emb, int B, int dim, cudaS
 // ---- K10: DDIM update + CFG combine ----------------------------------------------------------------
 __global__ void ddim_step_kernel(const float* __restrict__ x, const float* __restrict__ eps, float* __restrict__ xo,
                                  int64_t n, int cfg, float w, float sqrt_at, float sqrt_1mat, float sqrt_aprev,
-                                 float dir_coef, float sigma, const float* __restrict__ noise) {
+                                 float dir_coef, float sigma, const float* __restrict__ noise,
+                                 float* __restrict__ pred_x0) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   float e;
@@ -44,13 +45,14 @@ __global__ void ddim_step_kernel(const float* __restrict__ x, const float* __res
   float r = sqrt_aprev * x0 + dir_coef * e;
   if (noise) r += sigma * noise[i];
   xo[i] = r;
+  if (pred_x0) pred_x0[i] = x0;
 }
 
 int ddim_step_dispatch(const float* x, const float* eps, float* x_out, int64_t n, int cfg, float w, float a_t,
-                       float a_prev, float sigma, const float* noise, cudaStream_t st) {
+                       float a_prev, float sigma, const float* noise, float* pred_x0, cudaStream_t st) {
   const float dir = sqrtf(fmaxf(1.f - a_prev - sigma * sigma, 0.f));
   ddim_step_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(x, eps, x_out, n, cfg, w, sqrtf(a_t), sqrtf(1.f - a_t),
-                                                               sqrtf(a_prev), dir, sigma, noise);
+                                                               sqrtf(a_prev), dir, sigma, noise, pred_x0);
   TOPO_CUDA(cudaGetLastError());
   return 0;
 }

@@ -602,11 +602,7 @@ template <int BN, int STAGES, bool CONV>
 static int launch_gemm_pair(const GemmParams& p, cudaStream_t st) {
   using L = GemmSmem<BN, 0, STAGES, true>;
   auto kfn = gemm_kernel<BN, 0, STAGES, CONV, true>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    attr_set = true;
-  }
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
   GemmParams q = p;
   q.nt_total = 0;
   for (int i = 0; i < p.n_seg; ++i) q.nt_total += p.seg[i].n_tiles;
@@ -645,17 +641,8 @@ static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
   static_assert((BN == 128 || BN == 160 || BN == 192 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad), 160 / 192 / 256 (no LoRA)");
   auto kfn = gemm_kernel<BN, RPAD, STAGES, CONV>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    TOPO_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
-    attr_set = true;
-  }
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    TOPO_CUDA(cudaGetDevice(&dev));
-    TOPO_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  }
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
+  const int sms = sm_count();
   (void)grid;
   const int ctas = p.total_tiles < sms ? p.total_tiles : sms;  // persistent: one CTA per SM walks the tile list
   static int order = -1;  // TOPO_TILE_ORDER=m restores the m-fastest walk (tuning / A-B runs)
@@ -677,14 +664,7 @@ static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
 // GEGLU column interleave granularity the host must pack with (ops.geglu_interleave): values | gates per N tile.
 int gemm_geglu_tile(int N) { return (N % 256 == 0) ? 256 : 128; }
 
-static int sm_count() {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
-  }
-  return sms;
-}
+static int sm_count() { return device_sm_count(); }
 
 // 256-wide N tiles cut L2->SM operand traffic per FLOP by 25% and halve the number of MMA instructions; they need
 // enough tiles to keep every SM busy for at least two rounds.  TOPO_BN=128|256 overrides (experiments).

@@ -424,11 +424,8 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
   const int lanes = gn_lanes(vpr);
   const int rows = GN_THREADS / lanes;
   const size_t smem_s = (size_t)rows * 2 * C * sizeof(float);
-  static size_t smem_set = 48 * 1024;
-  if (smem_s > smem_set) {
-    TOPO_CUDA(cudaFuncSetAttribute(gn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
-    smem_set = smem_s;
-  }
+  if (smem_s > 48 * 1024)
+    if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(gn_stats_kernel), (int)smem_s)) return rc;
   int bps_s = 0;
   TOPO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps_s, gn_stats_kernel, GN_THREADS, smem_s));
   const int nitems = nsplit_s * B;

@@ -522,7 +522,9 @@ class Prepared:
 
 
 def fingerprint(model: nn.Module) -> Tuple:
-    """Changes whenever weights are written in place (load_state_dict bumps ``_version``) or modules are swapped."""
+    """Changes whenever weights are written in place through autograd-visible ops (``load_state_dict``, ``p.copy_()``
+    under ``no_grad`` bump ``_version``) or modules are swapped.  Writes through ``p.data`` are invisible to it: after
+    such an edit call ``model.invalidate_engine()``."""
     nv = np_ = 0
     dev = None
     for p in model.parameters():
@@ -648,8 +650,12 @@ class TopoEngine:
                 if side is None:
                     side = self.__dict__["_side"] = torch.cuda.Stream(device=x.device)
                 side.wait_stream(torch.cuda.current_stream(x.device))
-                with torch.cuda.stream(side):
-                    trunk = cnet_trunk()
+                ops.GN_SLOT[0] = 1          # the trunk's GroupNorms use their own statistics workspace
+                try:
+                    with torch.cuda.stream(side):
+                        trunk = cnet_trunk()
+                finally:
+                    ops.GN_SLOT[0] = 0
             else:
                 trunk = cnet_trunk()
 
@@ -887,7 +893,9 @@ class GraphedModel:
 
     ``t`` lives in a device buffer read by the timestep-embedding kernel, so ONE step graph serves every timestep.
     The kernels are captured on torch's capture stream through the C ABI's ``stream`` argument; TMA descriptors are
-    encoded on the host at capture time and baked into the graph as kernel parameters."""
+    encoded on the host at capture time and baked into the graph as kernel parameters.  Control states injected into
+    ``CrossAttention_LoRA_Control`` modules (``attention_lora.py:57-59``) are read through static copies that
+    ``set_cond`` refreshes, so a later ``inject_control_states`` with same-shaped tensors is honoured by the replay."""
 
     def __init__(self, eng: TopoEngine, Be: int, lat_hw: Tuple[int, int], ctx_shape: Tuple[int, int],
                  hint_hw: Optional[Tuple[int, int]], control_scales: Sequence[float], only_mid_control: bool,
@@ -900,29 +908,44 @@ class GraphedModel:
         # hint_batch < Be: the CFG halves share their control images (see TopoEngine.prepare)
         self.hint = None if hint_hw is None else torch.zeros(hint_batch or Be, 3, *hint_hw, device=dev)
         scales = [float(s) for s in control_scales]
-        side = torch.cuda.Stream(device=dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):  # warm-up outside capture: function attributes, workspaces, lazy inits
-            P = eng.prepare(self.ctx, self.hint)
-            eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=P, x_rep=x_rep)
-        torch.cuda.current_stream(dev).wait_stream(side)
-        torch.cuda.synchronize(dev)
-        n0 = LAUNCHES[0]
-        self.g_prep = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_prep):
-            self.P = eng.prepare(self.ctx, self.hint)
-        self.prep_launches = LAUNCHES[0] - n0
-        n0 = LAUNCHES[0]
-        self.g_step = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_step, pool=self.g_prep.pool()):
-            self.eps = eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=self.P,
-                                       x_rep=x_rep)
-        self.step_launches = LAUNCHES[0] - n0
+        self.ctrl = [(m, m.control_states.detach().to(dev).clone()) for m in eng.control_modules()
+                     if m.control_states is not None]
+        live = [m.control_states for m, _ in self.ctrl]
+        for m, buf in self.ctrl:
+            m.control_states = buf
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):  # warm-up outside capture: function attributes, workspaces, lazy inits
+                P = eng.prepare(self.ctx, self.hint)
+                eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=P, x_rep=x_rep)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            n0 = LAUNCHES[0]
+            self.g_prep = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_prep):
+                self.P = eng.prepare(self.ctx, self.hint)
+            self.prep_launches = LAUNCHES[0] - n0
+            n0 = LAUNCHES[0]
+            self.g_step = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_step, pool=self.g_prep.pool()):
+                self.eps = eng.apply_model(self.x, self.t, self.ctx, self.hint, scales, only_mid_control, prepared=self.P,
+                                           x_rep=x_rep)
+            self.step_launches = LAUNCHES[0] - n0
+        finally:
+            for (m, _), cs in zip(self.ctrl, live):
+                m.control_states = cs
 
     def set_cond(self, ctx: torch.Tensor, hint: Optional[torch.Tensor]) -> None:
         self.ctx.copy_(ctx, non_blocking=True)
         if self.hint is not None:
             self.hint.copy_(hint, non_blocking=True)
+        for m, buf in self.ctrl:
+            cs = m.control_states
+            if cs is None or tuple(cs.shape) != tuple(buf.shape):
+                raise capi.TopoError("GraphedModel.set_cond: control_states changed shape or were removed since this graph "
+                                     "was captured; fetch the graph again through TopoEngine.graphed()")
+            buf.copy_(cs, non_blocking=True)
         self.g_prep.replay()
         _count(self.prep_launches)
 
@@ -933,10 +956,27 @@ class GraphedModel:
         return self.eps
 
 
+def _control_modules(self: TopoEngine):
+    """Attention modules that can carry injected control states (``CrossAttention_LoRA_Control``), in execution order."""
+    out = []
+    for net in (self.unet, self.cnet):
+        for st in net.sts():
+            for blk in st.blocks:
+                for a in (blk.attn1, blk.attn2):
+                    if hasattr(a.module, "control_states"):
+                        out.append(a.module)
+    return out
+
+
 def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control,
-             hint_batch=None, x_rep=1) -> GraphedModel:
+             hint_batch=None, x_rep=1, branch: int = 0) -> GraphedModel:
+    """Cached step graph.  ``branch`` separates graphs of identical shape that must own distinct static buffers (the two
+    apply_model calls of ``cldm/ddim_hacked``: 0 = unconditional, 1 = conditional); the key also carries which attention
+    modules hold control states and their shapes, so injecting / removing control states selects another capture."""
+    ctrl_sig = tuple((i, tuple(m.control_states.shape)) for i, m in enumerate(self.control_modules())
+                     if m.control_states is not None)
     key = (Be, hint_batch or Be, tuple(lat_hw), tuple(ctx_shape), None if hint_hw is None else tuple(hint_hw),
-           tuple(float(s) for s in control_scales), bool(only_mid_control), int(x_rep))
+           tuple(float(s) for s in control_scales), bool(only_mid_control), int(x_rep), int(branch), ctrl_sig)
     cache = self.__dict__.setdefault("_graphs", {})
     if key not in cache:
         cache[key] = GraphedModel(self, Be, lat_hw, ctx_shape, hint_hw, control_scales, only_mid_control, hint_batch,
@@ -944,4 +984,5 @@ def _graphed(self: TopoEngine, Be, lat_hw, ctx_shape, hint_hw, control_scales, o
     return cache[key]
 
 
+TopoEngine.control_modules = _control_modules
 TopoEngine.graphed = _graphed

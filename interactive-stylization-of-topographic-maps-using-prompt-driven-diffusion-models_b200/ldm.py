@@ -93,8 +93,9 @@ class _NoForward(nn.Module):
 
 
 def zero_module(m: nn.Module) -> nn.Module:
-    for p in m.parameters():
-        p.detach().zero_()
+    with torch.no_grad():
+        for p in m.parameters():
+            p.zero_()
     return m
 
 
@@ -620,8 +621,11 @@ def randomize_zero_modules(model: nn.Module, seed: int = 1, std: float = 0.02) -
     with default init eps == 0 and any parity check would be vacuous."""
     g = torch.Generator().manual_seed(seed)
     n = 0
-    for name, p in sorted(model.named_parameters(), key=lambda kv: kv[0]):
-        if p.ndim >= 2 and not bool(p.detach().any()):
-            p.data.copy_(torch.randn(p.shape, generator=g) * std)
-            n += 1
+    with torch.no_grad():
+        for name, p in sorted(model.named_parameters(), key=lambda kv: kv[0]):
+            if p.ndim >= 2 and not bool(p.any()):
+                p.copy_((torch.randn(p.shape, generator=g) * std).to(p.device))   # bumps p._version: engines go stale
+                n += 1
+    if hasattr(model, "invalidate_engine"):
+        model.invalidate_engine()
     return n

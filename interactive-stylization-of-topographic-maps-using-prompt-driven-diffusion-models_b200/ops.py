@@ -188,12 +188,20 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp:
 
 
 _gn_ws = {}
+# Which of the (at most two) concurrent kernel streams of a step is issuing: 0 = main / UNet, 1 = the ControlNet trunk on
+# the engine's side stream.  The workspace is keyed on this slot, not on the stream handle, so the warm-up pass that
+# precedes a CUDA-graph capture (a different stream) creates the very buffers the capture uses: no process-global
+# tensor is ever allocated inside a graph's private memory pool.
+GN_SLOT = [0]
 
 
 def groupnorm_ws(B: int, G: int, device) -> torch.Tensor:
     n = capi.load_library().topo_groupnorm_ws_floats(B, G)
-    key = (str(device), n, capi.stream())   # one workspace per stream: the two networks of a step run concurrently
+    key = (str(device), n, GN_SLOT[0])
     if key not in _gn_ws:
+        if torch.cuda.is_current_stream_capturing():
+            raise capi.TopoError("groupnorm workspace requested for the first time inside a CUDA-graph capture; run the "
+                                 "same shapes once eagerly first (GraphedModel's warm-up does)")
         _gn_ws[key] = torch.zeros(n, dtype=torch.float32, device=device)  # the fused kernel's counters start at zero
     return _gn_ws[key]
 
@@ -240,8 +248,15 @@ def timestep_embedding(t: torch.Tensor, dim: int) -> torch.Tensor:
 
 
 def ddim_step(x: torch.Tensor, eps: torch.Tensor, cfg: bool, w: float, a_t: float, a_prev: float, sigma: float = 0.0,
-              noise: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+              noise: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+              pred_x0: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x' of one DDIM step (CFG combine fused); ``pred_x0`` (fp32, x-shaped) additionally receives the predicted x0."""
     xo = torch.empty_like(x) if out is None else out
+    if pred_x0 is not None:
+        capi.check(capi.load_library().topo_ddim_step_x0(
+            capi.handle(), x.data_ptr(), eps.data_ptr(), xo.data_ptr(), pred_x0.data_ptr(), x.numel(), int(cfg), w, a_t,
+            a_prev, sigma, capi.ptr(noise), capi.stream()), "topo_ddim_step_x0")
+        return xo
     capi.check(capi.load_library().topo_ddim_step(
         capi.handle(), x.data_ptr(), eps.data_ptr(), xo.data_ptr(), x.numel(), int(cfg), w, a_t, a_prev, sigma,
         capi.ptr(noise), capi.stream()), "topo_ddim_step")
@@ -444,6 +459,8 @@ def control_branch(attn, hidden: torch.Tensor, scale: float = 1.0, add_to: Optio
         c = nchw_to_nhwc(c).reshape(Bn, H * Wd, Cc)
     down, up = attn.to_control[0].weight, attn.to_control[1].weight  # [rc, C], [C, rc]
     rc, Cc = down.shape
+    if c.shape[-1] != Cc:   # the reference's nn.Linear raises here too (only batch / spatial mismatches are ignored)
+        raise capi.TopoError(f"to_control: control states have {c.shape[-1]} channels, the branch expects {Cc}")
     kp = ((rc + 63) // 64) * 64
     dpad = torch.zeros(kp, Cc, dtype=BF16, device=c.device)
     dpad[:rc] = down.to(BF16)

@@ -14,7 +14,6 @@ import numpy as np
 import torch
 
 from . import capi, ops
-from .engine import GraphedModel
 
 
 def make_ddim_timesteps(S: int, T: int = 1000) -> np.ndarray:
@@ -52,10 +51,22 @@ class DDIMSampler:
     def _cat_cond(uc: Dict, c: Dict) -> Dict:
         return {k: [torch.cat([uc[k][i], c[k][i]]) for i in range(len(c[k]))] for k in c}
 
+    # keyword arguments of ldm's ``DDIMSampler.sample`` that the reference never passes; a value other than the
+    # upstream default is refused instead of being silently dropped
+    _UNSUPPORTED = {"mask": None, "x0": None, "temperature": 1.0, "noise_dropout": 0.0, "score_corrector": None,
+                    "corrector_kwargs": None, "quantize_x0": False, "dynamic_threshold": None, "ucg_schedule": None,
+                    "normals_sequence": None, "timesteps": None}
+
     @torch.no_grad()
     def sample(self, S, batch_size, shape, conditioning=None, callback=None, img_callback=None, eta=0.0, x_T=None,
                verbose=False, log_every_t=100, unconditional_guidance_scale=1.0, unconditional_conditioning=None,
                **kwargs) -> Tuple[torch.Tensor, Dict[str, List[torch.Tensor]]]:
+        for k, v in kwargs.items():
+            if k not in self._UNSUPPORTED:
+                raise TypeError(f"DDIMSampler.sample: unexpected keyword argument {k!r}")
+            default = self._UNSUPPORTED[k]
+            if v is not None and not (isinstance(v, (bool, int, float)) and v == default):
+                raise capi.TopoError(f"DDIMSampler.sample: {k}={v!r} is not on the reference's path and is not implemented")
         model = self.model
         eng = model.engine()
         dev = eng.device
@@ -71,8 +82,12 @@ class DDIMSampler:
             hint = None if cond.get("c_concat") is None else torch.cat(cond["c_concat"], 1).to(dev, torch.float32)
             return ctx, hint
 
-        if cfg and not self.hacked:
+        two_calls = self.hacked
+        if cfg and not two_calls:
             uh, ch = unconditional_conditioning.get("c_concat"), conditioning.get("c_concat")
+            if (uh is None) != (ch is None):
+                two_calls = True   # guess mode (evaluateCN.py:86): the unconditional branch has no control -> cannot be batched
+        if cfg and not two_calls:
             shared = (uh is not None and ch is not None and len(uh) == len(ch)
                       and all(a is b for a, b in zip(uh, ch)))  # same control images for both CFG halves
             if shared:
@@ -90,21 +105,19 @@ class DDIMSampler:
         use_graph = bool(getattr(model, "use_cuda_graphs", True))
         if use_graph:
             runs = []
-            for ctx, hint in conds:
-                # the hacked variant needs two sets of static buffers: distinct graphs for the two branches
+            for br, (ctx, hint) in enumerate(conds):
+                # the two-call variant needs two sets of static buffers: one cached graph per branch
                 g = eng.graphed(ctx.shape[0], (H, W), tuple(ctx.shape[1:]), None if hint is None else tuple(hint.shape[2:]),
-                                scales, omc, None if hint is None else hint.shape[0], rep) if len(conds) == 1 else GraphedModel(
-                                    eng, ctx.shape[0], (H, W), tuple(ctx.shape[1:]),
-                                    None if hint is None else tuple(hint.shape[2:]), scales, omc)
+                                scales, omc, None if hint is None else hint.shape[0], rep, branch=br)
                 g.set_cond(ctx, hint)
                 runs.append(g)
         else:
             plans = [(ctx, hint, eng.prepare(ctx, hint)) for ctx, hint in conds]
 
-        inter = {"x_inter": [img], "pred_x0": []}
+        inter = {"x_inter": [img], "pred_x0": [img]}
         ts = self.ddim_timesteps
         n = len(ts)
-        for i in reversed(range(n)):
+        for i in reversed(range(n)):           # i = ldm's ``index`` (descending)
             if use_graph:
                 outs = []
                 for g in runs:
@@ -120,12 +133,17 @@ class DDIMSampler:
                 eps = outs[0] if len(outs) == 1 else torch.cat(outs)
             sig = float(self.ddim_sigmas[i])
             noise = torch.randn_like(img) if sig != 0.0 else None  # sigma = 0 (eta = 0) on every reference call
-            img = ops.ddim_step(img, eps, cfg, w, float(self.ddim_alphas[i]), float(self.ddim_alphas_prev[i]), sig, noise)
+            log = (i % log_every_t == 0) or (i == n - 1)            # ldm: ``index % log_every_t == 0 or index == total_steps - 1``
+            px0 = torch.empty_like(img) if (log or img_callback) else None
+            img = ops.ddim_step(img, eps, cfg, w, float(self.ddim_alphas[i]), float(self.ddim_alphas_prev[i]), sig, noise,
+                                pred_x0=px0)
             if callback:
                 callback(i)
-            step_no = n - 1 - i
-            if step_no % log_every_t == 0 or step_no == n - 1:
+            if img_callback:
+                img_callback(px0, i)
+            if log:
                 inter["x_inter"].append(img)
+                inter["pred_x0"].append(px0)
         return img, inter
 
 

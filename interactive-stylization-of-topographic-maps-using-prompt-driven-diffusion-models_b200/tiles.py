@@ -45,13 +45,19 @@ def stitch_tiles(tiles: torch.Tensor, cols: int) -> torch.Tensor:
     return tiles.reshape(rows, cols, h, w, C).permute(0, 2, 1, 3, 4).reshape(rows * h, cols * w, C).contiguous()
 
 
-def gather_tiles(local: torch.Tensor, n_tiles: int, group=None) -> torch.Tensor:
+def gather_tiles(local: torch.Tensor, n_tiles: int, group=None, world: Optional[int] = None) -> torch.Tensor:
     """All ranks contribute their uint8 slab ``[t_g, h, w, C]``; returns the full ``[T, h, w, C]`` on every rank.
-    Ragged shards are padded to the largest shard for the collective and trimmed afterwards."""
+    Ragged shards are padded to the largest shard for the collective and trimmed afterwards.  ``world`` (when given) is
+    the number of shards the caller split the map into: asking for more than one without an initialised process group
+    of that size is an error, not a silently partial mosaic."""
     import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+    have = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+    if world is not None and world != have:
+        raise RuntimeError(f"gather_tiles: the map was split {world} ways but the process group has {have} rank(s); "
+                           "initialise torch.distributed (NCCL) with one rank per shard")
+    if have == 1:
         return local
-    world = dist.get_world_size(group)
+    world = have
     sizes = [shard_range(n_tiles, r, world) for r in range(world)]
     mx = max(hi - lo for lo, hi in sizes)
     pad = local
@@ -64,14 +70,35 @@ def gather_tiles(local: torch.Tensor, n_tiles: int, group=None) -> torch.Tensor:
     return torch.cat(parts) if any(p.shape[0] != mx for p in parts) else out
 
 
+def start_latents(n: int, shape: Sequence[int], seed: int, device, noise: str = "shared", tile_offset: int = 0) -> torch.Tensor:
+    """Starting noise of ``n`` tiles whose GLOBAL indices are ``tile_offset .. tile_offset + n`` — a function of
+    ``(seed, global tile index)`` only, never of how the map is sharded or batched.
+
+    ``"shared"`` (default, the reference): ``BaseModel/evaluateCN.py:77-79`` calls ``seed_everything(seed)`` before EVERY
+    tile and samples with batch 1, so every tile starts from the same ``randn((1,4,h,w))`` drawn on the sampling device.
+    ``"per_tile"``: tile ``i`` draws from a generator seeded ``seed + i``."""
+    if noise == "shared":
+        g = torch.Generator(device=device).manual_seed(int(seed))
+        return torch.randn((1, *shape), generator=g, device=device).expand(n, *shape).contiguous()
+    if noise == "per_tile":
+        out = torch.empty((n, *shape), device=device)
+        for i in range(n):
+            g = torch.Generator(device=device).manual_seed(int(seed) + tile_offset + i)
+            out[i] = torch.randn(tuple(shape), generator=g, device=device)
+        return out
+    raise ValueError(f"noise must be 'shared' or 'per_tile', got {noise!r}")
+
+
 @torch.no_grad()
 def stylize_tiles(model, ctx: torch.Tensor, hints: torch.Tensor, x_T: Optional[torch.Tensor] = None, steps: int = 30,
                   scale: float = 7.5, eta: float = 0.0, batch: int = 8, seed: int = 1234, hacked: bool = False,
-                  uc: Optional[torch.Tensor] = None, out_host: Optional[torch.Tensor] = None) -> torch.Tensor:
+                  uc: Optional[torch.Tensor] = None, out_host: Optional[torch.Tensor] = None, noise: str = "shared",
+                  tile_offset: int = 0) -> torch.Tensor:
     """Stylize ``T`` tiles: ``ctx [T,77,768]``, ``hints [T,3,512,512]`` in [0,1], optional ``x_T [T,4,64,64]`` (any of
     them may live in (pinned) host memory — they are copied batch by batch).  Returns uint8 ``[T,512,512,3]`` on the
     model's device, or fills and returns ``out_host`` when given.  ``uc`` defaults to the all-zero context of
-    ``vis_metrics.py:425``."""
+    ``vis_metrics.py:425``.  Without ``x_T`` the starting noise comes from ``start_latents(seed, tile_offset + i)``:
+    the result of a tile does not depend on ``batch`` or on which rank owns it."""
     dev = next(model.parameters()).device
     T = hints.shape[0]
     outs: List[torch.Tensor] = []
@@ -81,14 +108,14 @@ def stylize_tiles(model, ctx: torch.Tensor, hints: torch.Tensor, x_T: Optional[t
         c = ctx[lo:hi].to(dev, torch.float32, non_blocking=True)
         h = hints[lo:hi].to(dev, torch.float32, non_blocking=True)
         u = torch.zeros_like(c) if uc is None else uc[lo:hi].to(dev, torch.float32, non_blocking=True)
+        lat = (4, h.shape[2] // 8, h.shape[3] // 8)
         if x_T is None:
-            torch.manual_seed(seed + lo)
-            xt = None
+            xt = start_latents(hi - lo, lat, seed, dev, noise, tile_offset + lo)
         else:
             xt = x_T[lo:hi].to(dev, torch.float32, non_blocking=True)
         cond = {"c_crossattn": [c], "c_concat": [h]}
         ucd = {"c_crossattn": [u], "c_concat": [h]}
-        z, _ = sampler.sample(S=steps, conditioning=cond, batch_size=hi - lo, shape=(4, h.shape[2] // 8, h.shape[3] // 8),
+        z, _ = sampler.sample(S=steps, conditioning=cond, batch_size=hi - lo, shape=lat,
                               unconditional_guidance_scale=scale, unconditional_conditioning=ucd, eta=eta, x_T=xt)
         u8 = model.engine().decode_to_u8(z)
         if out_host is not None:
@@ -104,8 +131,9 @@ def stylize_tiles(model, ctx: torch.Tensor, hints: torch.Tensor, x_T: Optional[t
 @torch.no_grad()
 def stylize_map(model, ctx: torch.Tensor, hints: torch.Tensor, cols: int, x_T: Optional[torch.Tensor] = None,
                 rank: int = 0, world: int = 1, group=None, **kw) -> torch.Tensor:
-    """Data-parallel full map: this rank stylizes its contiguous shard, one gather, stitch.  Returns the mosaic."""
+    """Data-parallel full map (``evaluateCN.py:60-120`` + ``stitchTiles.py:6-46``): this rank stylizes its contiguous
+    shard ``[lo, hi)`` of the row-major tile list, ONE gather, stitch.  Returns the mosaic on every rank."""
     T = hints.shape[0]
     lo, hi = shard_range(T, rank, world)
-    local = stylize_tiles(model, ctx[lo:hi], hints[lo:hi], None if x_T is None else x_T[lo:hi], **kw)
-    return stitch_tiles(gather_tiles(local, T, group), cols)
+    local = stylize_tiles(model, ctx[lo:hi], hints[lo:hi], None if x_T is None else x_T[lo:hi], tile_offset=lo, **kw)
+    return stitch_tiles(gather_tiles(local, T, group, world=world), cols)

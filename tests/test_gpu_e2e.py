@@ -4,11 +4,8 @@ identical seeded weights / hints / contexts / x_T (tests/synth.py), plus the ref
 Tolerances (bf16 storage, fp32 accumulation/statistics; BASELINE.json north_star):
   * eps of one apply_model:   cosine >= 0.9995 and max-abs <= 3e-2 * max|ref|
   * final decoded tile:       cosine >= 0.999                       (north_star: >= 0.999)
-  * per-step latents:         max-abs <= PER_STEP_REL * max|ref latent| with the oracle latent fed to both sides
-                              (teacher-forced, so the number is the error of ONE denoising step).  The north_star
-                              figure of 2e-2 is an absolute error on unit-scale latents; with random-init weights and
-                              CFG 7.5 the latents grow to |x| ~ 20 (bf16 spacing at 20 is already 0.125), so the bound
-                              is applied relative to the latent's magnitude.
+  * per-step latents:         tests/test_gpu_fullsize.py (2e-2 * max(1, max|x_ref|) at the configs' stated sizes, 2e-2
+                              absolute at unit scale, and the 4 coarse steps of configs[0] against an ideal bf16 pipeline)
 """
 import os
 
@@ -19,7 +16,6 @@ import synth
 from gpu_util import BF16
 
 pytestmark = pytest.mark.gpu
-PER_STEP_REL = 5e-2
 G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
@@ -108,21 +104,7 @@ def test_config1_sample_preview_parity():
         print(f"[parity] config1 final tile cos={cos:.6f} max_abs={(img - img_ref).abs().max().item():.3e}")
         assert img.shape == (1, 3, 512, 512) and float(img.min()) >= -1 and float(img.max()) <= 1
         assert cos >= 0.999
-        # teacher-forced per-step latents
-        ts, a, a_prev, _ = O.make_schedule(4)
-        eng = model.engine()
-        c2, h2 = torch.cat([torch.zeros_like(ctx), ctx]), torch.cat([hint, hint])
-        P = eng.prepare(c2, h2)
-        xs = [xT] + inter
-        for k, i in enumerate(reversed(range(4))):
-            x_in = xs[k]
-            t = torch.full((2,), int(ts[i]), device="cuda")
-            eps = eng.apply_model(torch.cat([x_in, x_in]), t, c2, h2, model.control_scales, False, prepared=P)
-            x_out = ops.ddim_step(x_in, eps, True, 7.5, float(a[i]), float(a_prev[i]))
-            err = (x_out - xs[k + 1]).abs().max().item()
-            mag = xs[k + 1].abs().max().item()
-            print(f"[parity] config1 step {k} (t={int(ts[i])}): latent max_abs={err:.3e} ref_max={mag:.3e} rel={err / mag:.3e}")
-            assert err <= PER_STEP_REL * max(1.0, mag)
+    # per-step latents of this config: tests/test_gpu_fullsize.py::test_config0_coarse_steps_vs_ideal_bf16_pipeline
 
 
 def test_ctrlora_30step_batch_and_u8_tiles():

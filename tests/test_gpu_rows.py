@@ -1,0 +1,218 @@
+"""-m gpu: rows of SURVEY.md §8 that round 1 left without a hardware test (VERDICT r1 "What's missing" 2-4):
+
+  a5   CrossAttention_LoRA_Control with injected control states (LoRA_modified/attention_lora.py:35-81), stand-alone and
+       inside apply_model after inject_control_lora_into_ldm (:107-137), incl. the shape-mismatch no-op (:77-80) and the
+       CUDA-graph path (static control buffers)
+  a5'  ControlLoRA three-conv hint encoder (attention_lora.py:87-101)
+  u9   cldm/ddim_hacked two-call CFG sampler as driven by BaseModel/evaluateCN.py:82-96 (scale 9, 20 steps, encoded
+       empty prompt as the unconditional context, guess_mode's c_concat=None branch)
+  u9'  model.sample_log, the CFG-free path of LoRA_modified/gen_test.py:113-116
+
+All comparisons are against oracle/ldm_oracle.py in fp32 on the same GPU (TF32 off); tolerances as in test_gpu_e2e.py.
+"""
+import pytest
+import torch
+
+import synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+
+
+def _cos(a, b):
+    return torch.nn.functional.cosine_similarity(a.float().flatten(), b.float().flatten(), dim=0).item()
+
+
+def _rel(a, b):
+    return (a.float() - b.float()).abs().max().item() / b.float().abs().max().item()
+
+
+def test_lora_control_attention_standalone():
+    """forward(x, context) of one CrossAttention_LoRA_Control: NCHW and token-shaped control states, the silent no-op
+    when the control shape does not match the output (attention_lora.py:77-80), and control_states=None."""
+    from oracle import ldm_oracle as O
+    from topo_b200 import lora
+    torch.manual_seed(3)
+    attn = lora.CrossAttention_LoRA_Control(query_dim=320, context_dim=768, heads=8, dim_head=40, lora_rank=4, control_rank=6)
+    for m in attn.modules():
+        if isinstance(m, lora.LoRALinear):
+            torch.nn.init.normal_(m.B.weight, std=0.05)
+    torch.nn.init.normal_(attn.to_control[1].weight, std=0.2)
+    attn = attn.cuda()
+    g = torch.Generator().manual_seed(4)
+    B, H, W = 2, 16, 16
+    x = torch.randn(B, H * W, 320, generator=g).cuda()
+    ctx = torch.randn(B, 77, 768, generator=g).cuda()
+    cs4 = torch.randn(B, 320, H, W, generator=g).cuda()
+    sd = {"a." + k: v.float() for k, v in attn.state_dict().items()}
+    xb, cb = x.bfloat16().float(), ctx.bfloat16().float()
+    with torch.no_grad():
+        base = attn(xb, cb)
+        ref0 = O.lora_control_attention(sd, "a", xb, cb, 8, None)
+        assert _rel(base, ref0) <= 2e-2
+        attn.inject_control_states(cs4)                                   # BCHW, flattened to B,HW,C by the module
+        y4 = attn(xb, cb, scale=0.7)
+        ref4 = O.lora_control_attention(sd, "a", xb, cb, 8, cs4.bfloat16().float(), 0.7)
+        attn.inject_control_states(cs4.permute(0, 2, 3, 1).reshape(B, H * W, 320).contiguous())   # token-shaped
+        y3 = attn(xb, cb, scale=0.7)
+        attn.inject_control_states(cs4[:, :, :8])                         # wrong spatial size -> no-op
+        ybad = attn(xb, cb, scale=0.7)
+        attn.inject_control_states(None)
+    e4, e3 = _rel(y4, ref4), _rel(y3, ref4)
+    print(f"[parity] LoRA-control attention: rel(4-D)={e4:.3e} rel(3-D)={e3:.3e} "
+          f"|ctrl|/|out|={(ref4 - ref0).abs().max().item() / ref0.abs().max().item():.2f}")
+    assert e4 <= 2e-2 and e3 <= 2e-2
+    assert _rel(y4, ref0) > 5e-2                                           # the control term is not negligible here
+    assert torch.equal(ybad, base)
+
+
+def test_control_lora_encoder():
+    from oracle import ldm_oracle as O
+    from topo_b200 import lora
+    torch.manual_seed(5)
+    enc = lora.ControlLoRA().cuda()
+    hint = synth.make_hint(2, 128).cuda()
+    sd = {"e." + k: v.float() for k, v in enc.state_dict().items()}
+    with torch.no_grad():
+        y = enc(hint)
+        ref = O.control_lora_encoder(sd, "e", hint)
+    err = _rel(y, ref)
+    print(f"[parity] ControlLoRA encoder {tuple(y.shape)}: rel={err:.3e} cos={_cos(y, ref):.6f}")
+    assert y.shape == ref.shape == (2, 256, 32, 32) and y.dtype == torch.float32
+    assert err <= 2e-2 and _cos(y, ref) >= 0.9995
+
+
+def _inject(model, lat, B, seed=21):
+    """inject_control_lora_into_ldm on the UNet + control states on four attentions: two that match their token shape
+    (added), one with a wrong spatial size and one with a wrong batch (both silently ignored by the reference; a wrong
+    CHANNEL count raises inside to_control on both sides).  States are scaled x10 so the zero-init-sized to_control
+    weights (N(0, 0.02^2) after randomize_zero_modules) move eps measurably."""
+    from topo_b200 import ldm, lora
+    unet = model.model.diffusion_model
+    n = lora.inject_control_lora_into_ldm(unet, rank=4, control_rank=4)
+    assert n == 32
+    ldm.randomize_zero_modules(model, seed=9)        # B matrices and to_control[1] are zero-initialised
+    model.cuda()
+    g = torch.Generator().manual_seed(seed)
+    states = {
+        "input_blocks.1.1.transformer_blocks.0.attn1": 10 * torch.randn(B, 320, lat, lat, generator=g),
+        "input_blocks.4.1.transformer_blocks.0.attn2": 10 * torch.randn(B, 640, lat // 2, lat // 2, generator=g),
+        "middle_block.1.transformer_blocks.0.attn1": 10 * torch.randn(B, 1280, lat // 4, lat // 4, generator=g),  # HW mismatch
+        "output_blocks.11.1.transformer_blocks.0.attn2": 10 * torch.randn(B + 1, 320, lat, lat, generator=g),    # B mismatch
+    }
+    ctrl = {}
+    for name, cs in states.items():
+        mod = unet.get_submodule(name)
+        assert isinstance(mod, lora.CrossAttention_LoRA_Control)
+        mod.inject_control_states(cs.cuda())
+        ctrl["model.diffusion_model." + name] = cs.cuda().bfloat16().float()
+    return ctrl
+
+
+def test_control_states_inside_apply_model_and_graph():
+    from oracle import ldm_oracle as O
+    from topo_b200 import sampling
+    model = synth.build_model("stock", with_vae=False)
+    B, lat = 2, 16
+    ctrl = _inject(model, lat, B)
+    sd = {k: v.float() for k, v in model.state_dict().items()}
+    scales = synth.lora_scales(model)
+    hint, ctx, x = synth.make_hint(B, lat * 8).cuda(), synth.make_ctx(B).cuda(), synth.make_xT(B, lat).cuda()
+    t = torch.tensor([601, 201], device="cuda")
+    cond = {"c_crossattn": [ctx], "c_concat": [hint]}
+    with torch.no_grad():
+        eps = model.apply_model(x, t, cond)
+        ref = O.apply_model(sd, x, t, cond, heads=8, scales=scales, ctrl=ctrl)
+        ref_off = O.apply_model(sd, x, t, cond, heads=8, scales=scales)
+    err, cos = _rel(eps, ref), _cos(eps, ref)
+    print(f"[parity] apply_model with control states: rel_max={err:.3e} cos={cos:.6f} "
+          f"(effect of the control branch on eps: {_rel(ref, ref_off):.3e})")
+    assert cos >= 0.9995 and err <= 3e-2
+    assert _rel(ref, ref_off) > 1e-2                                      # the branch is live, not a no-op
+    # CUDA-graph path, CFG-free (Be = B so the control shapes still match): two steps; then NEW control states of the same
+    # shape must be honoured by the cached graph (static copies refreshed in set_cond)
+    s = sampling.DDIMSampler(model)
+    with torch.no_grad():
+        z, _ = s.sample(S=2, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x)
+        zr, _ = O.ddim_sample(sd, 2, cond, None, x_T=x, scales=scales, ctrl=ctrl)
+        e1 = _rel(z, zr)
+        name = "model.diffusion_model.input_blocks.1.1.transformer_blocks.0.attn1"
+        new = (10 * torch.randn(B, 320, lat, lat, generator=torch.Generator().manual_seed(77))).cuda()
+        model.model.diffusion_model.get_submodule(name[len("model.diffusion_model."):]).inject_control_states(new)
+        ctrl2 = dict(ctrl)
+        ctrl2[name] = new.bfloat16().float()
+        n_graphs = len(model.engine()._graphs)
+        z2, _ = s.sample(S=2, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x)
+        zr2, _ = O.ddim_sample(sd, 2, cond, None, x_T=x, scales=scales, ctrl=ctrl2)
+        e2 = _rel(z2, zr2)
+    print(f"[parity] graph replay with control states: rel={e1:.3e}; after re-injection rel={e2:.3e} "
+          f"(stale would be {_rel(z, zr2):.3e})")
+    assert e1 <= 3e-2 and e2 <= 3e-2 and _rel(z, zr2) > 2 * e2
+    assert len(model.engine()._graphs) == n_graphs                        # same shapes -> the cached graph was reused
+
+
+def test_ddim_hacked_two_call_cfg_scale9_20steps():
+    """BaseModel/evaluateCN.py:82-96: cldm.ddim_hacked sampler (cond and uncond as two apply_model calls), scale 9.0,
+    20 steps, unconditional context = an encoded prompt (not zeros), strength-scaled control."""
+    from oracle import ldm_oracle as O
+    from topo_b200 import sampling
+    model = synth.build_model("stock", with_vae=False).cuda()
+    sd = {k: v.float() for k, v in model.state_dict().items()}
+    B, lat = 2, 16
+    hint, ctx, x = synth.make_hint(B, lat * 8).cuda(), synth.make_ctx(B).cuda(), synth.make_xT(B, lat).cuda()
+    uctx = synth.make_ctx(B, seed=501).cuda()                             # stands in for get_learned_conditioning([n_prompt])
+    cond = {"c_crossattn": [ctx], "c_concat": [hint]}
+    uc = {"c_crossattn": [uctx], "c_concat": [hint]}
+    model.control_scales = [0.9] * 13                                      # evaluateCN.py:91 `[strength] * 13`
+    s = sampling.DDIMSampler(model, hacked=True)
+    with torch.no_grad():
+        z, inter = s.sample(S=20, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x,
+                            unconditional_guidance_scale=9.0, unconditional_conditioning=uc, eta=0.0, log_every_t=5)
+        zr, ir = O.ddim_sample(sd, 20, cond, None, 9.0, uc, 0.0, x, hacked=True, control_scales=[0.9] * 13)
+        zb, _ = O.ddim_sample(sd, 20, cond, None, 9.0, uc, 0.0, x, hacked=False, control_scales=[0.9] * 13)
+        n_graphs = len(model.engine()._graphs)
+        z_again, _ = s.sample(S=20, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x,
+                              unconditional_guidance_scale=9.0, unconditional_conditioning=uc, eta=0.0)
+        n_graphs_again = len(model.engine()._graphs)
+        # guess mode (evaluateCN.py:84): the unconditional branch runs without control -> two calls even when not hacked
+        uc_g = {"c_crossattn": [uctx], "c_concat": None}
+        zg, _ = sampling.DDIMSampler(model).sample(S=4, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x,
+                                                   unconditional_guidance_scale=9.0, unconditional_conditioning=uc_g)
+        zgr, _ = O.ddim_sample(sd, 4, cond, None, 9.0, uc_g, 0.0, x, hacked=True, control_scales=[0.9] * 13)
+    cos, err = _cos(z, zr), _rel(z, zr)
+    print(f"[parity] ddim_hacked 20 steps scale 9: final latent cos={cos:.6f} rel_max={err:.3e} "
+          f"(two-call vs batched oracle: {_rel(zr, zb):.1e}); guess-mode 4 steps cos={_cos(zg, zgr):.6f}")
+    assert len(ir) == 20 and cos >= 0.999 and _cos(zg, zgr) >= 0.999
+    # ldm's intermediates: x_T, then every index with index % log_every_t == 0 or the first step
+    assert len(inter["x_inter"]) == len(inter["pred_x0"]) == 1 + 5 and torch.equal(inter["x_inter"][-1], z)
+    # two cached graphs (one per branch), reused by the second call (no re-capture per call)
+    assert n_graphs == 2 and n_graphs_again == 2 and torch.equal(z, z_again)
+    with pytest.raises(Exception):
+        s.sample(S=4, batch_size=B, shape=(4, lat, lat), conditioning=cond, x_T=x, mask=torch.ones(1))
+
+
+def test_sample_log_cfg_free():
+    """model.sample_log(cond, batch_size, ddim=True, ddim_steps, eta) — LoRA_modified/gen_test.py:113-116: no
+    unconditional branch, Be = B, x_T drawn from the global generator on the sampling device."""
+    from oracle import ldm_oracle as O
+    model = synth.build_model("qkvo", with_vae=False).cuda()
+    sd = {k: v.float() for k, v in model.state_dict().items()}
+    scales = synth.lora_scales(model)
+    B, lat = 2, 16
+    hint, ctx = synth.make_hint(B, lat * 8).cuda(), synth.make_ctx(B).cuda()
+    cond = {"c_crossattn": [ctx], "c_concat": [hint]}
+    with torch.no_grad():
+        torch.manual_seed(4321)
+        z, inter = model.sample_log(cond, B, ddim=True, ddim_steps=10, eta=0.0)
+        torch.manual_seed(4321)
+        xT = torch.randn((B, 4, lat, lat), device="cuda")
+        zr, _ = O.ddim_sample(sd, 10, cond, None, x_T=xT, scales=scales)
+    cos, err = _cos(z, zr), _rel(z, zr)
+    print(f"[parity] sample_log (CFG-free, 10 steps): cos={cos:.6f} rel_max={err:.3e}")
+    assert torch.equal(inter["x_inter"][0], xT) and z.shape == (B, 4, lat, lat)
+    assert cos >= 0.999 and err <= 5e-2

@@ -64,3 +64,37 @@ def test_gather_tiles_gloo_world2(T):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert all(ok for _, ok, _ in res), res
+
+
+@pytest.mark.parametrize("noise", ["shared", "per_tile"])
+def test_start_latents_depend_on_seed_and_global_index_only(noise):
+    """the starting noise of a tile must not change with the sharding (world) or the batch size."""
+    T, shape = 8, (4, 8, 8)
+
+    def assemble(world, batch):
+        parts = []
+        for r in range(world):
+            lo, hi = tiles.shard_range(T, r, world)
+            for b0 in range(lo, hi, batch):           # stylize_map passes tile_offset=lo, stylize_tiles adds its batch offset
+                n = min(hi, b0 + batch) - b0
+                parts.append(tiles.start_latents(n, shape, 1234, "cpu", noise, tile_offset=b0))
+        return torch.cat(parts)
+
+    ref = assemble(1, 8)
+    for world, batch in ((1, 4), (4, 8), (4, 1), (2, 3)):
+        assert torch.equal(assemble(world, batch), ref), (world, batch)
+    if noise == "shared":     # evaluateCN.py:77-79: seed_everything(seed) before every tile, batch 1 -> one latent for all tiles
+        g = torch.Generator().manual_seed(1234)
+        assert torch.equal(ref[5], torch.randn((1, *shape), generator=g)[0]) and torch.equal(ref[0], ref[7])
+    else:
+        assert not torch.equal(ref[0], ref[1])
+    assert not torch.equal(tiles.start_latents(1, shape, 1, "cpu", noise), tiles.start_latents(1, shape, 2, "cpu", noise))
+    with pytest.raises(ValueError):
+        tiles.start_latents(1, shape, 1, "cpu", "nope")
+
+
+def test_gather_refuses_a_sharded_map_without_process_group():
+    local = torch.zeros(2, 4, 4, 3, dtype=torch.uint8)
+    assert tiles.gather_tiles(local, 2) is local and tiles.gather_tiles(local, 2, world=1) is local
+    with pytest.raises(RuntimeError):
+        tiles.gather_tiles(local, 4, world=2)

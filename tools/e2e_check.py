@@ -5,7 +5,7 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 import torch
 torch.backends.cuda.matmul.allow_tf32 = False
 torch.backends.cudnn.allow_tf32 = False
-import synth
+from topo_b200 import synth
 from oracle import ldm_oracle as O
 from topo_b200.sampling import DDIMSampler
 

@@ -2,7 +2,8 @@
 import os, sys, collections
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
-import torch, synth
+import torch
+from topo_b200 import synth
 from topo_b200 import engine as E
 Be = int(sys.argv[1]) if len(sys.argv) > 1 else 38
 model = synth.build_model("ctrlora").cuda(); eng = model.engine(); B = Be // 2

@@ -5,7 +5,7 @@ import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 import torch
-import synth
+from topo_b200 import synth
 from topo_b200 import engine as E
 
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 19

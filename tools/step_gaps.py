@@ -3,7 +3,8 @@ stylize_tiles (CUDA events, Be=38)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
-import torch, synth
+import torch
+from topo_b200 import synth
 from topo_b200 import tiles
 from topo_b200.sampling import DDIMSampler
 

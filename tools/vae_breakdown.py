@@ -2,7 +2,8 @@
 import os, sys, collections
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
-import torch, synth
+import torch
+from topo_b200 import synth
 from topo_b200 import engine as E
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 19
 model = synth.build_model("ctrlora", control_lora_rank=16).cuda(); eng = model.engine()
