@@ -1,14 +1,16 @@
 #!/usr/bin/env python
 """bench.py — 512x512 map tiles/s of the ControlNet+LoRA SD-1.5 stylization hot path (BASELINE.json metric).
 
-  python bench.py --gpus N --steps K --warmup W            # this repo's sm_100a path
-  python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port) on host cores
+  python bench.py --gpus N --steps K --warmup W                 # this repo's sm_100a path, default workload
+  python bench.py --workload addlrSD|qkvo|fullmap ...           # the other BASELINE configs (not the driver's line)
+  python bench.py --impl reference --steps K --warmup W         # the reference's CPU path (oracle port) on host cores
 
-One "step" = one pass of the hot path over one batch of synthetic tiles: BASELINE.json configs[1] ("ctrlora":
-ControlNet qkvo LoRA rank 16, 19-prompt multiseg batch = 19 tiles of 512x512, nominal 30 DDIM steps = 31 model calls,
-classifier-free guidance 7.5 with the pair batched, VAE decode, uint8 conversion).  N > 1: every rank stylizes its own
-19 tiles (weak scaling, no collective in the denoising loop) and the finished uint8 tiles are all-gathered once per
-step for stitching.  Prints ONE JSON line on rank 0.
+Default workload = BASELINE.json configs[1] ("ctrlora": ControlNet qkvo LoRA rank 16, 19-prompt multiseg batch = 19 tiles
+of 512x512, nominal 30 DDIM steps = 31 model calls, classifier-free guidance 7.5 with the pair batched, VAE decode, uint8
+conversion).  One "step" = one pass of the hot path over one batch of synthetic tiles.  N > 1: every rank stylizes its own
+tiles (weak scaling, no collective in the denoising loop) and the finished uint8 tiles are all-gathered once per step.
+`--workload fullmap` is configs[4]: ONE 16x16 mosaic (256 tiles) sharded over the N ranks in contiguous row blocks, one
+all-gather, stitched on every rank — strong scaling.  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -18,24 +20,32 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+sys.path[:0] = [ROOT]
 
 METRIC = "512x512 map tiles/sec (30-step CN+LoRA SD1.5)"
 UNIT = "tiles/s"
-TILES, STEPS_DDIM, SCALE, RANK = 19, 30, 7.5, 16
-WORKLOAD = ("ctrlora (configs[1]): random-init SD1.5-arch UNet+ControlNet, ControlNet q/k/v/out LoRA rank 16, "
-            "19 tiles 512x512 per step, DDIM S=30 (31 model calls), CFG 7.5 batched [uncond;cond], VAE decode, uint8")
-# algorithmic work, SURVEY.md §8(d): per effective-batch element per apply_model with step-invariant work hoisted
-GFLOP_APPLY, GFLOP_HOIST, GFLOP_VAE = 1069.4, 14.72 + 4.31, 2514.5
-TFLOP_PER_TILE = (31 * 2 * GFLOP_APPLY + 2 * GFLOP_HOIST + GFLOP_VAE) / 1e3
-# dram__bytes_read.sum + dram__bytes_write.sum per launch (MB), mean over the launches of that class in the
-# `ncu --set full` capture of tools/profile_step.py (same Be=38 apply_model): profiles/r01g_ncu_full_gemm.txt (first 80
-# gemm_kernel launches: 62 projections, 18 convs) and profiles/r01e_ncu_full_attention.txt (Be=38 self-attention)
-NCU_TRAFFIC_MB = {"gemm": 173.2, "conv3x3": 89.3, "attn_self": 462.0}
+STEPS_DDIM = 30
+# algorithmic work, SURVEY.md §8(d): GFLOP per effective-batch element per apply_model with step-invariant work hoisted
+GFLOP_HOIST, GFLOP_VAE = 14.72 + 4.31, 2514.5
+WORKLOADS = {
+    # name: variant, model overrides, tiles per step per GPU, CFG scale, GFLOP per element-call (None: counted live), text
+    "ctrlora": dict(variant="ctrlora", kw=dict(control_lora_rank=16), tiles=19, scale=7.5, gflop=1069.4,
+                    text="ctrlora (configs[1]): random-init SD1.5-arch UNet+ControlNet, ControlNet q/k/v/out LoRA rank 16, "
+                         "19 tiles 512x512 per step, DDIM S=30 (31 model calls), CFG 7.5 batched [uncond;cond], VAE decode, uint8"),
+    "addlrSD": dict(variant="addlrSD", kw={}, tiles=8, scale=7.5, gflop=1072.8,
+                    text="addlrSD (configs[2]): ControlNet qkvo LoRA rank 32 + UNet lora_qkv(r_q=8, r_kv=8) (96 wraps, s=2), "
+                         "8 tiles 512x512 per step, DDIM S=30 (31 model calls), CFG 7.5 batched, VAE decode, uint8"),
+    "qkvo": dict(variant="qkvo", kw={}, tiles=8, scale=5.0, gflop=None,
+                 text="qkvo (configs[3]): stock ControlNet + UNet lora_attn_qkvo(r=8, s=4) (128 wraps), 8 tiles 512x512 per "
+                      "step, DDIM S=30 (31 model calls), CFG 5.0 batched, VAE decode, uint8"),
+    "fullmap": dict(variant="ctrlora", kw=dict(control_lora_rank=16), tiles=256, scale=7.5, gflop=1069.4,
+                    text="full map (configs[4]): one 8192x8192 sheet = 16x16 mosaic of 256 tiles 512x512, ctrlora rank 16, DDIM "
+                         "S=30 (31 model calls), CFG 7.5 batched, per-tile x_T (seed 1234 + tile index), tiles sharded over the "
+                         "ranks in contiguous row blocks (<= 32 tiles = Be 64 per batch), ONE all-gather, stitch"),
+}
 
 
 def peaks():
@@ -44,6 +54,13 @@ def peaks():
         d = json.load(open(p))
         return dict(src="measured", hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"])
     return dict(src="fallback", hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0)
+
+
+def ncu_table():
+    """profiles/r02_ncu.json (tools/ncu_named.sh + tools/ncu_summary.py json): per kernel template instance, the mean
+    of `ncu --set full` metrics over the captured launches of the FINAL build.  None when the file is absent."""
+    p = os.path.join(ROOT, "profiles", "r02_ncu.json")
+    return json.load(open(p)) if os.path.exists(p) else None
 
 
 class ClockSampler:
@@ -79,16 +96,16 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the oracle (CPU port of the reference's PyTorch path) on the host cores
 # ----------------------------------------------------------------------------------------------------------
-def cpu_reference(n_calls: int, warm: int):
+def cpu_reference(wl: dict, n_calls: int, warm: int):
     """Times ``n_calls`` apply_model calls at Be=2 (the CFG pair of ONE tile, 64x64 latent) + one VAE decode with the
     fp32 oracle on all host threads and extrapolates: tile time = 31 * t_call + t_vae (+ hint/K-V not hoisted: the
     reference recomputes them every call, and so does the oracle)."""
     import torch
-    import synth
     from oracle import ldm_oracle as O
+    from topo_b200 import synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    model = synth.build_model("ctrlora", control_lora_rank=RANK)
+    model = synth.build_model(wl["variant"], **wl["kw"])
     sd = {k: v.float() for k, v in model.state_dict().items()}
     scales = synth.lora_scales(model)
     del model
@@ -112,16 +129,28 @@ def cpu_reference(n_calls: int, warm: int):
                        f"{t_call:.2f} s/call) + 1 VAE decode ({t_vae:.2f} s); tile time extrapolated as 31*t_call + t_vae")
 
 
+def config_of(args, wl, world=1):
+    """The `config` object both arms print (same keys and values, so the driver can compare them)."""
+    full = args.workload == "fullmap"
+    return {"workload": wl["text"], "tiles_per_step_per_gpu": (wl["tiles"] // world) if full else wl["tiles"],
+            "model_calls_per_tile": 31, "effective_batch": 2 * (min(32, wl["tiles"] // world) if full else wl["tiles"]),
+            "l2": "working set per step (2.4 GB weights + activations) exceeds the 126 MB L2; no explicit flush",
+            "cuda_graphs": True,
+            "gather": ("all_gather of uint8 tiles once per step" if (world > 1 or full) else "none (1 GPU)")}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    r = cpu_reference(max(1, args.steps), max(0, min(args.warmup, 1)))
+    wl = WORKLOADS[args.workload]
+    r = cpu_reference(wl, max(1, args.steps), max(0, min(args.warmup, 1)))
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * r["t_call"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "note": "reference = oracle/ldm_oracle.py, the CPU fp32 restatement of the "
-                       "reference's PyTorch path (its own code is not importable: empty ControlNet/ctrlora submodules)"},
+            "scaling": "strong" if args.workload == "fullmap" else "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config_of(args, wl, max(1, args.gpus)),
+            "reference_note": "reference = oracle/ldm_oracle.py, the CPU fp32 restatement of the reference's PyTorch path (its "
+                              "own code is not importable: empty ControlNet/ctrlora submodules); one CPU process, all host threads",
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -130,13 +159,76 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------------------
 # this repo's arm
 # ----------------------------------------------------------------------------------------------------------
+def roofline_leg(E, eng, model, pk, ctx_d, hints_d, xT_d):
+    """One extra eager apply_model at the bench batch with every launch bracketed by CUDA events on the launching stream
+    (after the timed region, so the headline number carries no event overhead), keyed by kernel template instance."""
+    import torch
+    dev = ctx_d.device
+    B = ctx_d.shape[0]
+    c2 = torch.cat([torch.zeros_like(ctx_d), ctx_d])
+    h2 = torch.cat([hints_d, hints_d])
+    x2 = torch.cat([xT_d, xT_d])
+    t2 = torch.full((2 * B,), 501.0, device=dev)
+    P = eng.prepare(c2, hints_d)              # as the sampler does: one hint per tile, context-free prefix shared
+    for _ in range(2):
+        eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
+    torch.cuda.synchronize()
+    E.PROF.recs, E.PROF.on = [], True
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
+    t1.record()
+    torch.cuda.synchronize()
+    E.PROF.on = False
+    ncu = ncu_table() or {}
+
+    def row(v, name=None):
+        tensor = v["flops"] > 0
+        ach = (v["flops"] / 1e12 if tensor else v["bytes"] / 1e9) / (v["ms"] / 1e3)
+        peak = pk["tf_sust"] if tensor else pk["hbm"]
+        r = {"ms": round(v["ms"], 3), "launches": v["launches"], "bound": "tensor" if tensor else "hbm",
+             "achieved": round(ach, 1), "unit": "TFLOP/s" if tensor else "GB/s", "frac": round(ach / peak, 4),
+             "gbs": round(v["bytes"] / 1e6 / max(v["ms"], 1e-9), 1), "ops": sorted(v["kinds"])}
+        n = ncu.get("kernels", {}).get(name or "")
+        if n:
+            r["ncu"] = {k: n[k] for k in ("launches", "dram_bytes_per_launch", "tensor_pipe_pct", "dram_pct", "duration_us") if k in n}
+        return r
+
+    by_kernel = E.prof_summary(by="kernel")
+    by_kind = E.prof_summary(by="kind")
+    total = sum(d["ms"] for d in by_kernel.values())
+    top = max(by_kernel, key=lambda k: by_kernel[k]["ms"])
+    d = by_kernel[top]
+    r = row(d, top)
+    flops_all = sum(v["flops"] for v in by_kernel.values())
+    nk = ncu.get("kernels", {}).get(top)
+    roof = {"bound": r["bound"], "kernel": top, "achieved": r["achieved"], "peak": pk["tf_sust"] if r["bound"] == "tensor" else pk["hbm"],
+            "unit": r["unit"], "frac": r["frac"],
+            "traffic": nk["dram_bytes_per_launch"] if nk else None,
+            "traffic_source": (f"profiles/r02_ncu.json ({ncu.get('source', 'ncu --set full')}): mean dram__bytes_read.sum + "
+                               f"dram__bytes_write.sum over {nk['launches']} captured launches of this kernel") if nk else
+                              "no ncu capture of this kernel in profiles/r02_ncu.json",
+            "peak_source": pk["src"] + (" (sustained bf16)" if r["bound"] == "tensor" else " (copy)"),
+            "launches": d["launches"], "avg_launch_us": 1e3 * d["ms"] / d["launches"],
+            "algorithmic_per_launch": (d["flops"] if r["bound"] == "tensor" else d["bytes"]) / d["launches"],
+            "share_of_apply_model": d["ms"] / total,
+            "by_kernel": {k: row(v, k) for k, v in sorted(by_kernel.items(), key=lambda kv: -kv[1]["ms"])},
+            "by_op": {k: row(v) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1]["ms"])},
+            "how": f"one eager apply_model (Be={2 * B}) after the timed region, every launch bracketed by CUDA events on the "
+                   "launching stream and keyed by the kernel template instance the C ABI reports (topo_last_kernel); achieved "
+                   "= algorithmic FLOPs (true head dim / true LoRA rank) or bytes / summed duration; peak = MEASURED_PEAKS",
+            "apply_model_ms_eager_instrumented": t0.elapsed_time(t1)}
+    return roof, flops_all / (2 * B) / 1e9
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    import synth
     from topo_b200 import engine as E
-    from topo_b200 import tiles
+    from topo_b200 import synth, tiles
 
+    wl = WORKLOADS[args.workload]
+    full = args.workload == "fullmap"
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -148,19 +240,36 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     pk = peaks()
 
-    model = synth.build_model("ctrlora", control_lora_rank=RANK).to(dev)
+    model = synth.build_model(wl["variant"], **wl["kw"]).to(dev)
     eng = model.engine()
-    # synthetic tiles of this rank (weak scaling: TILES per rank), pinned host copies for the e2e leg
-    hints_h = synth.make_hint(TILES, 512, seed=7 + 1000 * rank).pin_memory()
-    ctx_h = synth.make_ctx(TILES, seed=11 + 1000 * rank).pin_memory()
-    xT_h = synth.make_xT(TILES, 64, seed=1234 + rank).pin_memory()
-    out_h = torch.empty(TILES, 512, 512, 3, dtype=torch.uint8).pin_memory()
-    hints_d, ctx_d, xT_d = hints_h.to(dev), ctx_h.to(dev), xT_h.to(dev)
-    kw = dict(steps=STEPS_DDIM, scale=SCALE, eta=0.0, batch=TILES)
+    T = wl["tiles"]
+    if full:
+        # one synthetic 8192^2 sheet, tiled row-major as BaseModel/datasetCreation00.py:32-59; this rank keeps its shard
+        lo, hi = tiles.shard_range(T, rank, world)
+        sheet = synth.make_hint(1, 8192, seed=7)[0].permute(1, 2, 0).contiguous()
+        hints_h = tiles.split_sheet(sheet, 512)[lo:hi].permute(0, 3, 1, 2).contiguous().pin_memory()
+        del sheet
+        ctx_h = synth.make_ctx(1, seed=11).expand(hi - lo, -1, -1).contiguous().pin_memory()    # one prompt for the whole sheet
+        xT_h = None                                                                              # per-tile seed 1234 + global index
+        n_local, batch = hi - lo, min(32, hi - lo)
+    else:
+        hints_h = synth.make_hint(T, 512, seed=7 + 1000 * rank).pin_memory()
+        ctx_h = synth.make_ctx(T, seed=11 + 1000 * rank).pin_memory()
+        xT_h = synth.make_xT(T, 64, seed=1234 + rank).pin_memory()
+        n_local, batch = T, T
+    out_h = torch.empty(n_local, 512, 512, 3, dtype=torch.uint8).pin_memory()
+    hints_d, ctx_d = hints_h.to(dev), ctx_h.to(dev)
+    xT_d = None if xT_h is None else xT_h.to(dev)
+    kw = dict(steps=STEPS_DDIM, scale=wl["scale"], eta=0.0, batch=batch)
+    if full:
+        kw.update(noise="per_tile", tile_offset=tiles.shard_range(T, rank, world)[0])
+    total_tiles = T if full else T * world
 
     def step_device():
         u8 = tiles.stylize_tiles(model, ctx_d, hints_d, xT_d, **kw)
-        return tiles.gather_tiles(u8, TILES * world) if world > 1 else u8
+        if full:
+            return tiles.stitch_tiles(tiles.gather_tiles(u8, T, world=world), 16)
+        return tiles.gather_tiles(u8, T * world) if world > 1 else u8
 
     def step_e2e():
         tiles.stylize_tiles(model, ctx_h, hints_h, xT_h, out_host=out_h, **kw)
@@ -190,69 +299,36 @@ def run_ours(args):
     clk = ClockSampler(local) if rank == 0 else None
     ms, launches = timed(step_device, args.steps)
     clocks = clk.stop() if clk else None
-    value = TILES * world * args.steps / (ms / 1e3)
+    value = total_tiles * args.steps / (ms / 1e3)
 
     step_e2e()  # warm the pinned-memory path
     ms_e2e, _ = timed(step_e2e, args.steps)
-    e2e = TILES * world * args.steps / (ms_e2e / 1e3)
-    h2d = hints_h.numel() * 4 + ctx_h.numel() * 4 + xT_h.numel() * 4
+    e2e = total_tiles * args.steps / (ms_e2e / 1e3)
+    h2d = hints_h.numel() * 4 + ctx_h.numel() * 4 + (0 if xT_h is None else xT_h.numel() * 4)
     d2h = out_h.numel()
 
-    # roofline leg: one extra apply_model at the bench batch with every launch bracketed by CUDA events on the
-    # launching stream (eager, not inside the timed region so the headline number carries no event overhead)
-    roof = None
+    roof = end_to_end = None
     if rank == 0:
-        c2 = torch.cat([torch.zeros_like(ctx_d), ctx_d])
-        h2 = torch.cat([hints_d, hints_d])
-        x2 = torch.cat([xT_d, xT_d])
-        t2 = torch.full((2 * TILES,), 501.0, device=dev)
-        P = eng.prepare(c2, hints_d)              # as the sampler does: one hint per tile, context-free prefix shared
-        for _ in range(2):
-            eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
-        torch.cuda.synchronize()
-        E.PROF.recs, E.PROF.on = [], True
-        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-        t0.record()
-        eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=2)
-        t1.record()
-        torch.cuda.synchronize()
-        E.PROF.on = False
-        summ = E.prof_summary()
-        total = sum(d["ms"] for d in summ.values())
-        top = max(summ, key=lambda k: summ[k]["ms"])
-        d = summ[top]
-        tensor = d["flops"] > 0
-        ach = (d["flops"] / 1e12 if tensor else d["bytes"] / 1e9) / (d["ms"] / 1e3)
-        peak = pk["tf_sust"] if tensor else pk["hbm"]
-        roof = {"bound": "tensor" if tensor else "hbm", "kernel": top, "achieved": ach, "peak": peak,
-                "unit": "TFLOP/s" if tensor else "GB/s", "frac": ach / peak,
-                "traffic": NCU_TRAFFIC_MB[top] * 1e6 if top in NCU_TRAFFIC_MB else None,
-                "traffic_source": "ncu --set full, mean DRAM read+write bytes per launch of this class (profiles/r01g_ncu_full_gemm.txt, r01e_ncu_full_attention.txt)",
-                "peak_source": pk["src"] + (" (sustained bf16)" if tensor else " (copy)"),
-                "launches": d["launches"], "avg_launch_us": 1e3 * d["ms"] / d["launches"],
-                "share_of_apply_model": d["ms"] / total,
-                "by_kernel": {k: {"ms": round(v["ms"], 3), "launches": v["launches"],
-                                  "tflops": round(v["flops"] / 1e9 / max(v["ms"], 1e-9), 1),
-                                  "gbs": round(v["bytes"] / 1e6 / max(v["ms"], 1e-9), 1)} for k, v in summ.items()},
-                "how": "one eager apply_model (Be=38) after the timed region, every launch bracketed by CUDA events on "
-                       "the launching stream; achieved = algorithmic FLOPs (true head dim / true LoRA rank) / summed duration",
-                "apply_model_ms_eager_instrumented": t0.elapsed_time(t1)}
-        end_to_end = {"achieved_tflops": value / world * TFLOP_PER_TILE, "frac_of_sustained_bf16":
-                      value / world * TFLOP_PER_TILE / pk["tf_sust"], "tflop_per_tile": TFLOP_PER_TILE}
+        nb = min(batch, ctx_d.shape[0])
+        xr = xT_d[:nb] if xT_d is not None else tiles.start_latents(nb, (4, 64, 64), 1234, dev, "per_tile", 0)
+        roof, gflop_live = roofline_leg(E, eng, model, pk, ctx_d[:nb], hints_d[:nb], xr)
+        gflop = wl["gflop"] or gflop_live
+        tflop_tile = (31 * 2 * gflop + 2 * GFLOP_HOIST + GFLOP_VAE) / 1e3
+        end_to_end = {"achieved_tflops": value / world * tflop_tile, "frac_of_sustained_bf16":
+                      value / world * tflop_tile / pk["tf_sust"], "tflop_per_tile": tflop_tile,
+                      "gflop_per_element_call": gflop, "gflop_per_element_call_counted_live": gflop_live,
+                      "gflop_source": "SURVEY.md §8(d)" if wl["gflop"] else "engine's per-launch algorithmic FLOP count"}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        r = cpu_reference(3, 1)
+        r = cpu_reference(wl, 3, 1)
         cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 1), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "tiles_per_step_per_gpu": TILES, "model_calls_per_tile": 31,
-                           "effective_batch": 2 * TILES, "l2": "working set per step (2.4 GB weights + activations) "
-                           "exceeds the 126 MB L2; no explicit flush", "cuda_graphs": True,
-                           "gather": "all_gather of uint8 tiles once per step" if world > 1 else "none (1 GPU)"},
+                "warmup": max(args.warmup, 1), "ms_per_step": ms / args.steps, "higher_is_better": True,
+                "scaling": "strong" if full else "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": config_of(args, wl, world),
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": ms_e2e / args.steps, "api": "topo_b200.tiles.stylize_tiles(pinned host in, host out)"},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roof, "end_to_end_roofline": end_to_end,
@@ -268,6 +344,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="ctrlora", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

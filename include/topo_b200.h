@@ -33,6 +33,9 @@ typedef struct topo_ctx* topo_handle_t;
 int topo_create(topo_handle_t* out, int device);
 int topo_destroy(topo_handle_t h);
 const char* topo_last_error(void);
+/* name of the kernel template instance the calling thread's last topo_* call launched (e.g. "gemm_kernel<256,0,6,1,1>"),
+ * as an ncu launch list spells it; diagnostic only */
+const char* topo_last_kernel(void);
 int topo_version(void);
 
 /* activation selectors for topo_linear_t.act */

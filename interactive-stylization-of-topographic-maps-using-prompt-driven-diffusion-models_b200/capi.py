@@ -19,7 +19,7 @@ ACT_NONE, ACT_SILU, ACT_GEGLU, ACT_GELU, ACT_RELU = 0, 1, 2, 3, 4
 
 # every symbol include/topo_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
-    "topo_create", "topo_destroy", "topo_last_error", "topo_version", "topo_lora_linear", "topo_conv3x3",
+    "topo_create", "topo_destroy", "topo_last_error", "topo_last_kernel", "topo_version", "topo_lora_linear", "topo_conv3x3",
     "topo_attention", "topo_attention_varlen", "topo_embed_sum", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
     "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_ddim_step_x0", "topo_conv_direct",
     "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_tile_metrics", "topo_im2col3x3_s1_k64",
@@ -58,6 +58,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
             "(nvcc, sm_100a). The B200 path has no PyTorch/CPU fallback.")
     lib = C.CDLL(path)
     lib.topo_last_error.restype = C.c_char_p
+    lib.topo_last_kernel.restype = C.c_char_p
     lib.topo_version.restype = C.c_int
     lib.topo_create.argtypes = [C.POINTER(C.c_void_p), C.c_int]
     lib.topo_destroy.argtypes = [C.c_void_p]
@@ -94,6 +95,10 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
 
 def last_error() -> str:
     return load_library().topo_last_error().decode()
+
+
+def last_kernel() -> str:
+    return load_library().topo_last_kernel().decode()
 
 
 def check(rc: int, what: str = "") -> None:

@@ -325,6 +325,7 @@ static int launch_attention(const AttnParams& p, int B, cudaStream_t st) {
   dim3 grid((p.Nq + ATT_BM * NS - 1) / (ATT_BM * NS), p.heads, B);
   kfn<<<grid, L::THREADS, L::TOTAL, st>>>(p);
   TOPO_CUDA(cudaGetLastError());
+  note_kernel("attention_kernel<%d, %d, %d, %d>", DP, NS, NPOLY, (int)EARLY);
   return 0;
 }
 

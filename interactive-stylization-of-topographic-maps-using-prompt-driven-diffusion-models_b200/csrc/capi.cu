@@ -22,6 +22,15 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static thread_local char g_kernel[128] = "";
+
+void note_kernel(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_kernel, sizeof(g_kernel), fmt, ap);
+  va_end(ap);
+}
+
 int ensure_dyn_smem(const void* kernel, int bytes) {
   static std::mutex mu;
   static std::map<std::pair<int, const void*>, int> done;
@@ -157,6 +166,7 @@ extern "C" {
 
 int topo_version(void) { return TOPO_VERSION; }
 const char* topo_last_error(void) { return g_err; }
+const char* topo_last_kernel(void) { return g_kernel; }
 
 int topo_create(topo_handle_t* out, int device) {
   if (!out) {

@@ -42,6 +42,9 @@ int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims
 int ensure_dyn_smem(const void* kernel, int bytes);
 // SM count of the CURRENT device (cached per device)
 int device_sm_count();
+// name of the kernel (template instance) the calling thread's last dispatch launched: topo_last_kernel() returns it, so the
+// host-side per-launch timing (bench.py's roofline leg) is keyed by the same names an ncu launch list shows
+void note_kernel(const char* fmt, ...);
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

@@ -623,6 +623,7 @@ static int launch_gemm_pair(const GemmParams& p, cudaStream_t st) {
   cfg.attrs = at;
   cfg.numAttrs = 1;
   TOPO_CUDA(cudaLaunchKernelEx(&cfg, kfn, q));
+  note_kernel("gemm_kernel<%d, 0, %d, %d, 1>", BN, STAGES, (int)CONV);
   return 0;
 }
 
@@ -658,6 +659,7 @@ static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   }
   kfn<<<ctas, GEMM_THREADS, L::TOTAL, st>>>(q);
   TOPO_CUDA(cudaGetLastError());
+  note_kernel("gemm_kernel<%d, %d, %d, %d, 0>", BN, RPAD, STAGES, (int)CONV);
   return 0;
 }
 

@@ -416,6 +416,7 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
       gn_small_kernel<16><<<grid, GN_THREADS, smem, st>>>(reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y),
                                                            y_ld, HW, C, G, chunk, gamma, beta, eps, apply_silu);
     TOPO_CUDA(cudaGetLastError());
+    note_kernel("gn_small_kernel<%d>", maxv);
     return 0;
   }
   const int ppb_s = gn_stats_ppb(HW, C);
@@ -442,6 +443,7 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
       reinterpret_cast<const bf16*>(x), x_ld, reinterpret_cast<bf16*>(y), y_ld, HW, C, G, ppb, nsplit_s, ws, gamma, beta,
       eps, apply_silu);
   TOPO_CUDA(cudaGetLastError());
+  note_kernel("gn_stats_kernel+gn_apply_kernel");
   return 0;
 }
 
@@ -597,6 +599,7 @@ static void launch_ln_group(const bf16* x, int x_ld, bf16* y, int y_ld, int M, c
   static const bool persistent = [] { const char* e = getenv("TOPO_LN_PERSIST"); return !e || atoi(e) != 0; }();
   const int grid = (persistent && nblk > 148 * bps) ? 148 * bps : nblk;
   layernorm_group_kernel<G, V><<<grid, 256, 0, st>>>(x, x_ld, y, y_ld, M, gamma, beta, eps);
+  note_kernel("layernorm_group_kernel<%d, %d>", G, V);
 }
 
 int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld, int M, int C,

@@ -55,15 +55,18 @@ def _rec(kind: str, flops: float, nbytes: float, fn, tag: str = ""):
     e0.record()
     r = fn()
     e1.record()
-    PROF.recs.append((kind, flops, nbytes, e0, e1, tag))
+    PROF.recs.append((kind, flops, nbytes, e0, e1, tag, capi.last_kernel()))
     return r
 
 
-def prof_summary() -> Dict[str, Dict[str, float]]:
-    """kind -> {launches, ms, flops, bytes}; call after torch.cuda.synchronize()."""
+def prof_summary(by: str = "kind") -> Dict[str, Dict[str, float]]:
+    """``by='kind'``: op class -> {launches, ms, flops, bytes}; ``by='kernel'``: the same keyed by the kernel template
+    instance the C side launched (the names of an ncu launch list).  Call after torch.cuda.synchronize()."""
     out: Dict[str, Dict[str, float]] = {}
-    for kind, fl, nb, e0, e1, _tag in PROF.recs:
-        d = out.setdefault(kind, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0))
+    for kind, fl, nb, e0, e1, _tag, kern in PROF.recs:
+        key = kind if by == "kind" else (kern or kind)
+        d = out.setdefault(key, dict(launches=0, ms=0.0, flops=0.0, bytes=0.0, kinds=set()))
+        d["kinds"].add(kind)
         d["launches"] += 1
         d["ms"] += e0.elapsed_time(e1)
         d["flops"] += fl

@@ -8,7 +8,8 @@ from topo_b200 import synth
 
 Be = int(sys.argv[1]) if len(sys.argv) > 1 else 38
 dev = "cuda"
-model = synth.build_model("ctrlora").to(dev)
+variant = sys.argv[2] if len(sys.argv) > 2 else "ctrlora"
+model = synth.build_model(variant).to(dev)
 eng = model.engine()
 B = Be // 2
 ctx = synth.make_ctx(B).to(dev); hint = synth.make_hint(B).to(dev); xT = synth.make_xT(B).to(dev)

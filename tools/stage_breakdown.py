@@ -47,7 +47,7 @@ torch.cuda.synchronize()
 E.PROF.on = False
 tot = 0.0
 rows = {}
-for kind, fl, nb, e0, e1, tag in E.PROF.recs:
+for kind, fl, nb, e0, e1, tag, kern in E.PROF.recs:
     ms = e0.elapsed_time(e1)
     d = rows.setdefault((kind, tag), [0, 0.0, 0.0, 0.0])
     d[0] += 1; d[1] += ms; d[2] += fl; d[3] += nb
@@ -66,7 +66,7 @@ eng.apply_model(x2, t2, c2, h2, model.control_scales, False, prepared=P, x_rep=X
 torch.cuda.synchronize()
 E.PROF.on = False
 rows, tot = {}, 0.0
-for kind, fl, nb, e0, e1, tag in E.PROF.recs:
+for kind, fl, nb, e0, e1, tag, kern in E.PROF.recs:
     ms = e0.elapsed_time(e1)
     d = rows.setdefault((kind, tag), [0, 0.0, 0.0, 0.0])
     d[0] += 1; d[1] += ms; d[2] += fl; d[3] += nb

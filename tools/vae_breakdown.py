@@ -17,7 +17,7 @@ with torch.no_grad():
     E.PROF.recs, E.PROF.on = [], True
     eng.decode_to_u8(z); torch.cuda.synchronize(); E.PROF.on = False
 agg = collections.defaultdict(lambda: [0, 0.0, 0.0, 0.0])
-for kind, fl, nb, a, b, tag in E.PROF.recs:
+for kind, fl, nb, a, b, tag, kern in E.PROF.recs:
     r = agg[(kind, tag)]; r[0] += 1; r[1] += a.elapsed_time(b); r[2] += fl; r[3] += nb
 tot = sum(r[1] for r in agg.values())
 print(f"instrumented total {tot:.2f} ms over {sum(r[0] for r in agg.values())} launches")
