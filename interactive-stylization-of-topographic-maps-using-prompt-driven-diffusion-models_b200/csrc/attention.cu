@@ -317,6 +317,315 @@ attention_kernel(const __grid_constant__ AttnParams p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// K3 — cross-attention over a SHORT key sequence (the 77-token prompt; Nk <= 80), HBM bound: q in, o out, nothing else.
+//
+// The flash kernel above treats the prompt as two 64-key blocks and pays, per 128-query tile, a CTA launch, a TMEM
+// allocation, barrier initialisation, a K/V load and an online-softmax rescale for 24 KB of useful traffic (146 us at
+// B38 N4096 d40 against a 37 us byte floor, 22 % of HBM peak: profiles/r01e_ncu_full_attention.txt).  Here
+//   * the kernel is PERSISTENT: the (batch, head, query tile) list is cut into one contiguous, equally long range per
+//     resident CTA; K and V of a (batch, head) (80 x dp, zero rows past Nk) are loaded once per range segment into one of
+//     two shared-memory buffers (the next segment's K/V arrive while the current one is still in use), TMEM is allocated
+//     once, the query tiles stream through a TMA ring;
+//   * all keys fit one UMMA (M=128, N=80, K=dp), so softmax is ONE pass with the exact row maximum — no running max, no O
+//     rescale; P (bf16 pairs) is written over the S columns it was computed from and consumed by a TS-mode UMMA
+//     (O = P V, M=128, N=dp, K=80, V MN-major straight from its TMA tile);
+//   * NWG softmax warpgroups work on alternate tiles, each with its own TMEM slot [S/P 80 | O dp]; the single MMA-issuer
+//     thread issues S(i+NWG) right behind P V(i), so a warpgroup's next S is ready before it has finished storing O(i).
+// Per tile and SM the byte floor is ~900 clk (24 KB at 44 GB/s/SM), the MUFU needs 640 clk (128 x 80 exponentials at
+// 16/clk) and the issue slots ~400 clk, so with >= 4 tiles in flight per SM the kernel sits on the HBM roofline.
+// warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2.. = NWG x 4 softmax/epilogue warps.
+constexpr int XA_NKP = 80;  // keys per tile, padded: UMMA N (multiple of 16) and P's K extent
+
+template <int DP, int NWG>
+struct XAttnSmem {
+  static constexpr int THREADS = 32 * (2 + 4 * NWG);
+  static constexpr int ATOMS = (DP + 63) / 64;
+  static constexpr int Q_ATOM = ATT_BM * 128, KV_ATOM = XA_NKP * 128;
+  static constexpr int Q_BYTES = ATOMS * Q_ATOM, KV_BYTES = ATOMS * KV_ATOM;
+  static constexpr int QS = DP <= 64 ? 4 : (DP <= 80 ? 3 : 2);         // query tiles in flight
+  static constexpr int KV_OFF = QS * Q_BYTES;                          // [2 buffers][K | V]
+  static constexpr int BAR_OFF = KV_OFF + 4 * KV_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256;
+  static constexpr uint32_t O_COL = XA_NKP;                            // slot: S fp32 [0,80) (P bf16x2 over [0,40)) | O fp32 [80, 80+DP)
+  static constexpr uint32_t SLOT_COLS = O_COL + ((DP + 15) / 16) * 16;
+  static constexpr uint32_t TMEM_COLS = NWG * SLOT_COLS <= 256 ? 256 : 512;
+  static constexpr int CTAS = 512 / TMEM_COLS;
+  static_assert(NWG * SLOT_COLS <= 512, "TMEM");
+  static_assert(CTAS * (TOTAL + 1024) <= 228 * 1024, "smem");
+};
+
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+
+template <int DP, int NWG>
+__global__ void __launch_bounds__(XAttnSmem<DP, NWG>::THREADS, XAttnSmem<DP, NWG>::CTAS)
+cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group, long long total_tiles) {
+  using L = XAttnSmem<DP, NWG>;
+  constexpr int ATOMS = L::ATOMS, QS = L::QS;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* q_ring = smem;
+  uint8_t* kv_buf = smem + L::KV_OFF;   // buffer u: K at u * 2 * KV_BYTES, V right behind it
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* kv_full = bars;             // [2]
+  uint64_t* kv_empty = bars + 2;        // [2] every UMMA of the segment that used the buffer has finished
+  uint64_t* q_full = bars + 4;          // [QS]
+  uint64_t* q_empty = q_full + QS;      // [QS] S(i) finished reading the stage
+  uint64_t* s_full = q_empty + QS;      // [NWG] S complete in the slot
+  uint64_t* p_ready = s_full + NWG;     // [NWG] 128 arrivals: P written over S
+  uint64_t* o_full = p_ready + NWG;     // [NWG] P V complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + NWG);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  // this CTA's contiguous range [g0, g0 + n) of the flat (group = batch * heads + head, tile) list
+  const long long g0 = total_tiles * blockIdx.x / gridDim.x;
+  const int n = (int)(total_tiles * (blockIdx.x + 1) / gridDim.x - g0);
+  const int grp0 = (int)(g0 / tiles_per_group);
+  auto seg_of = [&](int i) { return (int)((g0 + i) / tiles_per_group) - grp0; };   // K/V segment index of local tile i
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_q);
+    tma_prefetch_desc(&p.tm_k);
+    tma_prefetch_desc(&p.tm_v);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+    }
+    for (int i = 0; i < QS; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+    }
+    for (int i = 0; i < NWG; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_ready[i], 128);
+      mbar_init(&o_full[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, L::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer: K/V per segment (double buffered), the query tiles through a ring ==========
+    if (lane == 0) {
+      int seg_loaded = -1;
+      for (int i = 0; i < n; ++i) {
+        const long long g = g0 + i;
+        const int grp = (int)(g / tiles_per_group), tile = (int)(g - (long long)grp * tiles_per_group);
+        const int b = grp / p.heads, col0 = (grp - b * p.heads) * DP;
+        const int seg = grp - grp0;
+        if (seg != seg_loaded) {
+          const int u = seg & 1;
+          mbar_wait(&kv_empty[u], ((seg >> 1) & 1) ^ 1);
+          mbar_expect_tx(&kv_full[u], 2 * L::KV_BYTES);
+          uint8_t* kd = kv_buf + u * 2 * L::KV_BYTES;
+#pragma unroll
+          for (int a = 0; a < ATOMS; ++a) {
+            tma_load_3d(kd + a * L::KV_ATOM, &p.tm_k, &kv_full[u], col0 + a * 64, 0, b);
+            tma_load_3d(kd + L::KV_BYTES + a * L::KV_ATOM, &p.tm_v, &kv_full[u], col0 + a * 64, 0, b);
+          }
+          seg_loaded = seg;
+        }
+        const int qs = i % QS;
+        mbar_wait(&q_empty[qs], ((i / QS) & 1) ^ 1);
+        mbar_expect_tx(&q_full[qs], L::Q_BYTES);
+#pragma unroll
+        for (int a = 0; a < ATOMS; ++a)
+          tma_load_3d(q_ring + qs * L::Q_BYTES + a * L::Q_ATOM, &p.tm_q, &q_full[qs], col0 + a * 64, tile * ATT_BM, b);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, XA_NKP, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DP, 0, 1);  // B (= V) is MN-major
+      int seg_ready = -1;   // highest segment whose K/V this thread has already waited for
+      auto issue_s = [&](int i) {
+        const int seg = seg_of(i), u = seg & 1;
+        if (seg > seg_ready) {
+          mbar_wait(&kv_full[u], (seg >> 1) & 1);
+          seg_ready = seg;
+        }
+        const int qs = i % QS;
+        mbar_wait(&q_full[qs], (i / QS) & 1);
+        tc_fence_after();
+        const uint32_t q_s = smem_u32(q_ring + qs * L::Q_BYTES);
+        const uint32_t k_s = smem_u32(kv_buf + u * 2 * L::KV_BYTES);
+        const uint32_t tmem_s = tmem_base + (i % NWG) * L::SLOT_COLS;
+#pragma unroll
+        for (int k = 0; k < DP / 16; ++k) {
+          const uint64_t qd = kmajor_desc(q_s + (k >> 2) * L::Q_ATOM + (k & 3) * 32, 128);
+          const uint64_t kd = kmajor_desc(k_s + (k >> 2) * L::KV_ATOM + (k & 3) * 32, 128);
+          umma_bf16(tmem_s, qd, kd, idesc_s, k != 0);
+        }
+        umma_commit(&s_full[i % NWG]);
+        umma_commit(&q_empty[qs]);
+      };
+      for (int i = 0; i < NWG && i < n; ++i) issue_s(i);
+      for (int i = 0; i < n; ++i) {
+        const int slot = i % NWG;
+        const int seg = seg_of(i), u = seg & 1;
+        mbar_wait(&p_ready[slot], (i / NWG) & 1);
+        tc_fence_after();
+        const uint32_t v_s = smem_u32(kv_buf + u * 2 * L::KV_BYTES + L::KV_BYTES);
+        const uint32_t tmem_p = tmem_base + slot * L::SLOT_COLS;
+        const uint32_t tmem_o = tmem_p + L::O_COL;
+#pragma unroll
+        for (int k = 0; k < XA_NKP / 16; ++k)   // A = P straight from TMEM: 16 keys = 8 packed columns per step
+          umma_bf16_ts(tmem_o, tmem_p + k * 8, mnmajor_sw128_desc(v_s + k * 2048, L::KV_ATOM), idesc_pv, k != 0);
+        umma_commit(&o_full[slot]);
+        // last tile of its K/V segment: the buffer is free once everything issued so far has finished (the S of later
+        // segments issued ahead read the OTHER buffer)
+        if (i + 1 == n || seg_of(i + 1) != seg) umma_commit(&kv_empty[u]);
+        // S of this slot's NEXT tile goes in right behind P V (the tensor pipe executes in issue order, so it overwrites P
+        // only after P V has consumed it); the warpgroup is still storing O(i) when it completes
+        if (i + NWG < n) issue_s(i + NWG);
+      }
+    }
+  } else {
+    // ===================== softmax + epilogue warpgroups =====================
+    const int wg = (warp - 2) >> 2;
+    const int qd = warp & 3;  // the TMEM lane quadrant a warp can reach is warp % 4
+    const int row = qd * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    const uint32_t tmem_s = tmem_base + wg * L::SLOT_COLS + lane_addr;
+    const uint32_t tmem_o = tmem_s + L::O_COL;
+    const float c = p.scale_log2e;
+    const int Nk = p.Nk;
+    for (int i = wg; i < n; i += NWG) {
+      const uint32_t ph = ((i - wg) / NWG) & 1;
+      mbar_wait(&s_full[wg], ph);
+      tc_fence_after();
+      // ---- pass 1: exact row maximum over the Nk real keys (columns >= Nk hold q . 0 = 0 and are excluded)
+      float mx = -INFINITY;
+      {
+        float v[32];
+        tmem_ld32(tmem_s, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, (j < Nk) ? v[j] : -INFINITY);
+        tmem_ld32(tmem_s + 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, (32 + j < Nk) ? v[j] : -INFINITY);
+        float w[16];
+        tmem_ld16(tmem_s + 64, w);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) mx = fmaxf(mx, (64 + j < Nk) ? w[j] : -INFINITY);
+      }
+      const float nm = -mx * c;
+      // ---- pass 2: P = exp2(s c - m c) as packed bf16 pairs written over the S columns already consumed
+      float l = 0.f;
+      {
+        float v[32];
+        uint32_t pk[16];
+        tmem_ld32(tmem_s, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float e0 = (j < Nk) ? fast_exp2(fmaf(v[j], c, nm)) : 0.f;
+          const float e1 = (j + 1 < Nk) ? fast_exp2(fmaf(v[j + 1], c, nm)) : 0.f;
+          l += e0 + e1;
+          pk[j >> 1] = pack_bf16x2(e0, e1);
+        }
+        tmem_st16u(tmem_s, pk);
+        tmem_ld32(tmem_s + 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float e0 = (32 + j < Nk) ? fast_exp2(fmaf(v[j], c, nm)) : 0.f;
+          const float e1 = (33 + j < Nk) ? fast_exp2(fmaf(v[j + 1], c, nm)) : 0.f;
+          l += e0 + e1;
+          pk[j >> 1] = pack_bf16x2(e0, e1);
+        }
+        tmem_st16u(tmem_s + 16, pk);
+        float w[16];
+        tmem_ld16(tmem_s + 64, w);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const float e0 = (64 + j < Nk) ? fast_exp2(fmaf(w[j], c, nm)) : 0.f;
+          const float e1 = (65 + j < Nk) ? fast_exp2(fmaf(w[j + 1], c, nm)) : 0.f;
+          l += e0 + e1;
+          pk[j >> 1] = pack_bf16x2(e0, e1);
+        }
+        tmem_st8(tmem_s + 32, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&p_ready[wg]);
+      // ---- epilogue: O / l -> bf16 -> global (row per thread, 2 x 16 bytes per 16 columns)
+      const float inv = 1.0f / l;
+      const long long g = g0 + i;
+      const int grp = (int)(g / tiles_per_group), tile = (int)(g - (long long)grp * tiles_per_group);
+      const int b = grp / p.heads, col0 = (grp - b * p.heads) * DP;
+      const int qrow = tile * ATT_BM + row;
+      bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
+      mbar_wait(&o_full[wg], ph);
+      tc_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < DP; c0 += 16) {
+        float t[16];
+        tmem_ld16(tmem_o + c0, t);
+        tmem_ld_wait();
+        if (qrow < p.Nq) {
+          uint4 u0, u1;
+          u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
+          u0.z = pack_bf16x2(t[4] * inv, t[5] * inv);   u0.w = pack_bf16x2(t[6] * inv, t[7] * inv);
+          u1.x = pack_bf16x2(t[8] * inv, t[9] * inv);   u1.y = pack_bf16x2(t[10] * inv, t[11] * inv);
+          u1.z = pack_bf16x2(t[12] * inv, t[13] * inv); u1.w = pack_bf16x2(t[14] * inv, t[15] * inv);
+          *reinterpret_cast<uint4*>(dst + c0) = u0;
+          *reinterpret_cast<uint4*>(dst + c0 + 8) = u1;
+        }
+      }
+      // O(i) is out of TMEM before this warpgroup's next p_ready arrival, which is what lets the issuer start P V(i + NWG)
+      tc_fence_before();
+    }
+    __syncwarp();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, L::TMEM_COLS);
+  }
+}
+
+template <int DP, int NWG>
+static int launch_cross_attention(const AttnParams& p, int B, cudaStream_t st) {
+  using L = XAttnSmem<DP, NWG>;
+  auto kfn = cross_attention_kernel<DP, NWG>;
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
+  const int tiles_per_group = (p.Nq + ATT_BM - 1) / ATT_BM;
+  const long long total = (long long)tiles_per_group * p.heads * B;
+  // persistent: one CTA per resident slot (never more CTAs than would get at least NWG tiles each)
+  long long ctas = (long long)device_sm_count() * L::CTAS;
+  const long long want = (total + NWG - 1) / NWG;
+  if (ctas > want) ctas = want;
+  kfn<<<dim3((unsigned)ctas), L::THREADS, L::TOTAL, st>>>(p, tiles_per_group, total);
+  TOPO_CUDA(cudaGetLastError());
+  note_kernel("cross_attention_kernel<%d, %d>", DP, NWG);
+  return 0;
+}
+
 template <int DP, int NS, int NPOLY, bool EARLY = true>
 static int launch_attention(const AttnParams& p, int B, cudaStream_t st) {
   using L = AttnSmem<DP, NS, EARLY>;
@@ -389,6 +698,21 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   p.heads = heads;
   p.ldo = ldo;
   p.scale_log2e = scale * 1.4426950408889634f;
+  // short key sequences (the 77-token prompt): the K/V-resident single-pass kernel.  TOPO_XATTN=0 keeps the flash kernel.
+  static const bool xattn = [] { const char* e = getenv("TOPO_XATTN"); return !(e && e[0] == '0'); }();
+  if (xattn && kv_len == nullptr && Nk <= XA_NKP && Nq >= ATT_BM && dp != 64) {
+    uint64_t dims[3] = {cols, (uint64_t)Nk, (uint64_t)B};
+    uint64_t strk[2] = {(uint64_t)ldk * 2, (uint64_t)ldk * 2 * Nk};
+    uint64_t strv[2] = {(uint64_t)ldv * 2, (uint64_t)ldv * 2 * Nk};
+    uint32_t bx[3] = {64, (uint32_t)XA_NKP, 1};
+    int rc = make_tmap(&p.tm_k, k, 3, dims, strk, bx, 128);
+    if (rc) return rc;
+    rc = make_tmap(&p.tm_v, v, 3, dims, strv, bx, 128);
+    if (rc) return rc;
+    if (dp == 48) return launch_cross_attention<48, 2>(p, B, st);
+    if (dp == 80) return launch_cross_attention<80, 3>(p, B, st);
+    return launch_cross_attention<160, 2>(p, B, st);
+  }
   const int np = attn_npoly(dp);
   const int ns = attn_streams(dp, Nq);
   if (dp == 48) {
