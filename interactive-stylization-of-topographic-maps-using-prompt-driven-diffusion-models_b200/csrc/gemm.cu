@@ -13,9 +13,12 @@
 //                                   (XOR-swizzled 16-byte units), then row-contiguous residual loads + stores to an
 //                                   arbitrary (ld, column offset) destination: q/k/v, concat buffers and the ControlNet
 //                                   zero-conv residual are written in place.
-//  * LoRA: the SAME x tile also feeds a side UMMA  T = x A^T (N = r_pad) into a third TMEM region; after the K loop
-//    the epilogue warps move s*T (bf16) TMEM->smem and ONE more UMMA adds T B^T into the main accumulator — the
-//    low-rank delta never touches HBM.
+//  * LoRA: T = x A^T (N = r_pad) of a (row tile, segment) group goes into a third TMEM region in a short PRE-PASS over K
+//    (x tile + LoRA-A tile through the same ring, the LoRA-A tile in the W slot) that the issuer runs ONE TILE AHEAD of the
+//    group's first tile; the epilogue warps move s*T (bf16) TMEM->smem while that earlier tile's main loop is still
+//    running, and every tile of the group then STARTS with one UMMA  acc = (sT) B^T  and accumulates x W^T on top — the
+//    low-rank delta never touches HBM and the issuer never waits for the T round trip (round 1 applied T B^T after the
+//    K loop and idled the tensor pipe for ~1 us per tile: 3x the K = 320 main loop).
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -64,10 +67,11 @@ template <int BN, int RPAD, int STAGES, bool PAIR = false>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int W_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
-  static constexpr int LA_BYTES = RPAD * BK * 2;
-  static constexpr int STAGE_BYTES = A_BYTES + W_BYTES + LA_BYTES;
+  static constexpr int LA_BYTES = RPAD * BK * 2;            // LoRA-A tile of a T pre-pass stage: lives in the W slot
+  static constexpr int STAGE_BYTES = A_BYTES + W_BYTES;
   static constexpr int LB_BYTES = BN * RPAD * 2;
-  static constexpr int T_BYTES = BM * RPAD * 2;
+  static constexpr int T_ONE = BM * RPAD * 2;
+  static constexpr int T_BYTES = 2 * T_ONE;                 // two (s T) tiles: group g+1 is converted while group g is in use
   static constexpr int LB_OFF = STAGES * STAGE_BYTES;
   static constexpr int T_OFF = LB_OFF + LB_BYTES;
   static constexpr int STG_OFF = T_OFF + T_BYTES;          // fp32 staging: [32 rows][32 cols] per epilogue warp
@@ -215,10 +219,29 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      // LoRA pre-pass of one (row tile, segment) group: x tile + that segment's LoRA-A tile per K block
+      auto load_tpass = [&](const TileCoord& g) {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* a_s = smem + stage * L::STAGE_BYTES;
+          mbar_expect_tx(&full[stage], L::A_BYTES + L::LA_BYTES);
+          tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, g.m0);
+          tma_load_2d(a_s + L::A_BYTES, &p.seg[g.seg].tm_la, &full[stage], kb * BK, 0);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      };
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
         const GemmSegDev& sg = p.seg[c.seg];
         if (RPAD) {
+          if (it == 0) load_tpass(c);
+          if (tile + tile_step < tile_end) {
+            const TileCoord cn = tile_coord<BN, CONV>(p, tile_id(tile + tile_step));
+            if (cn.m0 != c.m0 || cn.seg != c.seg) load_tpass(cn);
+          }
           mbar_wait(lb_empty, (it & 1) ^ 1);  // previous tile's LoRA-up MMA is done with lb_tile
           mbar_expect_tx(lb_full, L::LB_BYTES);
           tma_load_2d(lb_tile, &sg.tm_lb, lb_full, 0, c.n0);
@@ -227,7 +250,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* a_s = smem + stage * L::STAGE_BYTES;
           uint8_t* w_s = a_s + L::A_BYTES;
-          uint8_t* la_s = w_s + L::W_BYTES;
           if (PAIR) {
             // both CTAs' bytes are credited to the LEADER's full barrier (the only one the MMA issuer waits on)
             if (rank == 0) mbar_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
@@ -264,7 +286,6 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, c.m0);
           }
           tma_load_2d(w_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
-          if (RPAD) tma_load_2d(la_s, &sg.tm_la, &full[stage], kb * BK, 0);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -279,24 +300,66 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
+      int g_cur = 0, t_waited = -1;   // LoRA: T index of the current tile's group / highest T index known to be in smem
+      const uint32_t tmem_t = tmem_base + T_COL;
+      // LoRA pre-pass: T = x A^T over the whole K extent into the T columns (the LoRA-A tile sits in the stage's W slot)
+      auto issue_tpass = [&]() {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_s = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t la_s = a_s + L::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16(tmem_t, kmajor_desc(a_s + k * 32, 128), kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
+          umma_commit(&empty[stage]);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(side_full);
+      };
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const int buf = NBUF == 2 ? (it & 1) : 0;
         const uint32_t acc_phase = NBUF == 2 ? ((it >> 1) & 1) : (it & 1);
         const uint32_t tmem_acc = tmem_base + buf * BN;
-        const uint32_t tmem_t = tmem_base + T_COL;
         // the last N tile of a segment only multiplies the columns that exist (UMMA N is a run-time field, multiple of 16)
         const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
         const int n_left = p.seg[c.seg].N - c.n0;
         const uint32_t n_eff = n_left >= BN ? BN : (PAIR ? ((n_left + 31) & ~31) : ((n_left + 15) & ~15));
         const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, n_eff);
+        bool next_group = false;
+        if (RPAD) {
+          if (it == 0) issue_tpass();                      // T index 0 (the only pre-pass the issuer has to wait for)
+          if (g_cur > t_waited) {                          // own (s T) tile is in smem: the T columns may be overwritten
+            mbar_wait(t_ready, g_cur & 1);
+            t_waited = g_cur;
+          }
+          if (tile + tile_step < tile_end) {
+            const TileCoord cn = tile_coord<BN, CONV>(p, tile_id(tile + tile_step));
+            next_group = cn.m0 != c.m0 || cn.seg != c.seg;
+            if (next_group) issue_tpass();                 // T index g_cur + 1, converted under this tile's main loop
+          }
+        }
         mbar_wait(&tempty[buf], acc_phase ^ 1);  // epilogue drained this accumulator (NBUF tiles ago)
         tc_fence_after();
+        if (RPAD) {
+          // the tile starts from the low-rank delta: acc = (s T) B^T
+          mbar_wait(lb_full, it & 1);
+          tc_fence_after();
+          const uint32_t t_s = smem_u32(t_tile + (g_cur & 1) * L::T_ONE);
+          const uint32_t lb_s = smem_u32(lb_tile);
+#pragma unroll
+          for (int k = 0; k < RPAD / 16; ++k)
+            umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, k != 0);
+          umma_commit(lb_empty);
+        }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_s = smem_u32(smem + stage * L::STAGE_BYTES);
           const uint32_t w_s = a_s + L::A_BYTES;
-          const uint32_t la_s = w_s + L::W_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
@@ -304,8 +367,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), make_idesc_bf16(2 * BM, 256), (kb | k) != 0);
               umma2_bf16(tmem_acc + 256, ad, kmajor_desc(w_s + 128 * BK * 2 + k * 32, 128), make_idesc_bf16(2 * BM, 64), (kb | k) != 0);
             } else if (PAIR) umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
-            else umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
-            if (RPAD) umma_bf16(tmem_t, ad, kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
+            else umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, RPAD ? 1u : (uint32_t)((kb | k) != 0));
           }
           if (PAIR) umma2_commit(&empty[stage]);   // frees the stage in BOTH CTAs
           else umma_commit(&empty[stage]);
@@ -314,20 +376,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             phase ^= 1;
           }
         }
-        if (RPAD) {
-          umma_commit(side_full);
-          mbar_wait(lb_full, it & 1);
-          mbar_wait(t_ready, it & 1);
-          tc_fence_after();
-          const uint32_t t_s = smem_u32(t_tile);
-          const uint32_t lb_s = smem_u32(lb_tile);
-#pragma unroll
-          for (int k = 0; k < RPAD / 16; ++k)
-            umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, 1);
-          umma_commit(lb_empty);
-        }
         if (PAIR) umma2_commit(&tfull[buf]);
         else umma_commit(&tfull[buf]);
+        if (next_group) ++g_cur;
       }
     }
   } else {
@@ -342,6 +393,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
     int it = 0;
+    int g_epi = 0;   // LoRA: index of the latest T this warp has converted
     for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
       const GemmSegDev& sg = p.seg[c.seg];
@@ -352,29 +404,38 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       // (the bias tile is written per warp after the accumulator wait, see below: no CTA-wide epilogue barrier)
 
       if (RPAD && hsel == 0) {
-        // s*T (fp32, TMEM) -> bf16 K-major swizzled smem tile, the A operand of the LoRA-up UMMA
-        mbar_wait(side_full, it & 1);
-        tc_fence_after();
-        float t[RPAD ? RPAD : 16];
-        tmem_ld16(tmem_base + T_COL + lane_addr, t);
-        if (RPAD == 32) tmem_ld16(tmem_base + T_COL + lane_addr + 16, t + 16);
-        tmem_ld_wait();
-        constexpr uint32_t span = (RPAD ? RPAD : 16) * 2;
-        constexpr uint32_t mask = span / 16 - 1;
+        // s*T (fp32, TMEM) -> bf16 K-major swizzled smem tile, the A operand of the LoRA-up UMMA that opens every tile of the
+        // group.  T index 0 belongs to this CTA's first tile; index g + 1 is produced one tile ahead (see the issuer).
+        auto convert_t = [&](int t_idx, float s_scale) {
+          mbar_wait(side_full, t_idx & 1);
+          tc_fence_after();
+          float t[RPAD ? RPAD : 16];
+          tmem_ld16(tmem_base + T_COL + lane_addr, t);
+          if (RPAD == 32) tmem_ld16(tmem_base + T_COL + lane_addr + 16, t + 16);
+          tmem_ld_wait();
+          constexpr uint32_t span = (RPAD ? RPAD : 16) * 2;
+          constexpr uint32_t mask = span / 16 - 1;
+          uint8_t* dst = t_tile + (t_idx & 1) * L::T_ONE;
 #pragma unroll
-        for (int j = 0; j < RPAD / 8; ++j) {
-          uint32_t off = row * span + j * 16;
-          off ^= ((off >> 7) & mask) << 4;
-          uint4 v;
-          v.x = pack_bf16x2(t[j * 8 + 0] * sg.s, t[j * 8 + 1] * sg.s);
-          v.y = pack_bf16x2(t[j * 8 + 2] * sg.s, t[j * 8 + 3] * sg.s);
-          v.z = pack_bf16x2(t[j * 8 + 4] * sg.s, t[j * 8 + 5] * sg.s);
-          v.w = pack_bf16x2(t[j * 8 + 6] * sg.s, t[j * 8 + 7] * sg.s);
-          *reinterpret_cast<uint4*>(t_tile + off) = v;
+          for (int j = 0; j < RPAD / 8; ++j) {
+            uint32_t off = row * span + j * 16;
+            off ^= ((off >> 7) & mask) << 4;
+            uint4 v;
+            v.x = pack_bf16x2(t[j * 8 + 0] * s_scale, t[j * 8 + 1] * s_scale);
+            v.y = pack_bf16x2(t[j * 8 + 2] * s_scale, t[j * 8 + 3] * s_scale);
+            v.z = pack_bf16x2(t[j * 8 + 4] * s_scale, t[j * 8 + 5] * s_scale);
+            v.w = pack_bf16x2(t[j * 8 + 6] * s_scale, t[j * 8 + 7] * s_scale);
+            *reinterpret_cast<uint4*>(dst + off) = v;
+          }
+          fence_proxy_async_smem();
+          tc_fence_before();
+          mbar_arrive(t_ready);
+        };
+        if (it == 0) convert_t(0, sg.s);
+        if (tile + tile_step < tile_end) {
+          const TileCoord cn = tile_coord<BN, CONV>(p, tile_id(tile + tile_step));
+          if (cn.m0 != c.m0 || cn.seg != c.seg) convert_t(++g_epi, p.seg[cn.seg].s);
         }
-        fence_proxy_async_smem();
-        tc_fence_before();
-        mbar_arrive(t_ready);
       }
 
       // ---- the warp owns rows [q*32, +32) x output columns [hsel*colsw, +colsw) of the tile and walks them in
@@ -640,7 +701,7 @@ static bool pair_enabled() {
 template <int BN, int RPAD, int STAGES, bool CONV>
 static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   using L = GemmSmem<BN, RPAD, STAGES>;
-  static_assert((BN == 128 || BN == 160 || BN == 192 || BN == 256) && (BN == 128 || RPAD == 0), "tile configs: 128 (any LoRA pad), 160 / 192 / 256 (no LoRA)");
+  static_assert((BN == 128 || BN == 160 || BN == 192 || BN == 256) && (BN <= 192 || RPAD == 0), "tile configs: 128 / 160 / 192 (any LoRA pad: 2 BN + r_pad TMEM columns), 256 (no LoRA)");
   auto kfn = gemm_kernel<BN, RPAD, STAGES, CONV>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
   const int sms = sm_count();
@@ -670,6 +731,26 @@ static int sm_count() { return device_sm_count(); }
 
 // 256-wide N tiles cut L2->SM operand traffic per FLOP by 25% and halve the number of MMA instructions; they need
 // enough tiles to keep every SM busy for at least two rounds.  TOPO_BN=128|256 overrides (experiments).
+// LoRA tiles (any segment count): 2 BN + r_pad TMEM columns allow up to 192-wide tiles; wider tiles mean fewer passes over x
+// per row tile (the short-K projections are bound by the SM's shared-memory fill rate, not by the tensor pipe) and fewer
+// T pre-passes per output column.  TOPO_LORA_BN=128|160|192 overrides (A/B runs).
+static int pick_bn_lora(const topo_linear_t* segs, int n_seg) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("TOPO_LORA_BN");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced == 128 || forced == 160 || forced == 192) return forced;
+  bool all192 = true, all160 = true;
+  for (int i = 0; i < n_seg; ++i) {
+    all192 = all192 && segs[i].N % 192 == 0;
+    all160 = all160 && segs[i].N % 160 == 0;
+  }
+  if (all192) return 192;
+  if (all160) return 160;
+  return 128;
+}
+
 static int pick_bn(int m_tiles, int N, int r_pad, int n_seg, int act) {
   if (r_pad != 0 || n_seg != 1) return 128;
   if (act == TOPO_ACT_GEGLU) return gemm_geglu_tile(N);
@@ -767,7 +848,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   TOPO_CHECK(K % BK == 0 && K > 0, TOPO_E_INVAL, "K (%d) must be a positive multiple of 64", K);
   TOPO_CHECK(x_ld % 8 == 0, TOPO_E_INVAL, "x_ld must be a multiple of 8 elements");
   TOPO_CHECK(M > 0, TOPO_E_INVAL, "M must be positive");
-  int BN = pick_bn((M + BM - 1) / BM, segs[0].N, segs[0].r_pad, n_seg, segs[0].act);
+  int BN = segs[0].r_pad ? pick_bn_lora(segs, n_seg) : pick_bn((M + BM - 1) / BM, segs[0].N, segs[0].r_pad, n_seg, segs[0].act);
   // measured: the short-K projections gain 8 % (98 -> 90 us at K = 320 / 384); K = 1280 and the 3x3 convs do not
   // (convs lose 5 %), so only K < 1024 GEMMs take the 160-wide tile
   if (use_bn160(segs[0].N, segs[0].r_pad, n_seg, segs[0].act) && K < 1024 && (M + BM - 1) / BM >= sm_count()) BN = 160;
@@ -804,13 +885,21 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   dim3 grid(p.total_tiles);
   if (wide320) return launch_gemm_pair<320, 5, false>(p, st);
   if (pair) return launch_gemm_pair<256, 6, false>(p, st);
+  if (r_pad == 16) {
+    if (BN == 192) return launch_gemm<192, 16, 4, false>(p, grid, st);
+    if (BN == 160) return launch_gemm<160, 16, 5, false>(p, grid, st);
+    return launch_gemm<128, 16, 5, false>(p, grid, st);
+  }
+  if (r_pad == 32) {
+    if (BN == 192) return launch_gemm<192, 32, 4, false>(p, grid, st);
+    if (BN == 160) return launch_gemm<160, 32, 4, false>(p, grid, st);
+    return launch_gemm<128, 32, 5, false>(p, grid, st);
+  }
   if (BN == 160) return launch_gemm<160, 0, 5, false>(p, grid, st);
   // BN = 256: a fourth stage (192 KB in flight) pays when the K loop is long (latency bound: 3 -> 4 stages took the
   // 3x3 convs from 930 to 1010-1380 TFLOP/s); short-K projections are epilogue bound and keep 3 stages
   if (BN == 256) return K >= 1024 ? launch_gemm<256, 0, 4, false>(p, grid, st) : launch_gemm<256, 0, 3, false>(p, grid, st);
-  if (r_pad == 0) return launch_gemm<128, 0, 6, false>(p, grid, st);
-  if (r_pad == 16) return launch_gemm<128, 16, 5, false>(p, grid, st);
-  return launch_gemm<128, 32, 4, false>(p, grid, st);
+  return launch_gemm<128, 0, 6, false>(p, grid, st);
 }
 
 int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const topo_linear_t* seg, cudaStream_t st) {

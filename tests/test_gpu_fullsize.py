@@ -11,7 +11,7 @@ Gates (BASELINE.json north_star):
   * per-step latent, teacher-forced (the oracle's latent of step k is fed to the kernels, so the number is the error of
     ONE denoising step): max-abs <= 2e-2 * max(1, max|x_ref|)   — the north-star figure read relative to the latent's
     magnitude once it exceeds one (random-init weights + CFG push |x| to ~20, where one bf16 ulp is already 0.125)
-  * unit scale (guidance 1.0, |x| = O(1)): the same 2e-2 as an ABSOLUTE bound on every step of the 30-step schedule
+  * guidance 1.0 (no CFG amplification): the same 2e-2 as an ABSOLUTE bound on every step of the 30-step schedule
   * configs[0]'s 4 coarse steps (t = 751 -> 501 moves the latent by 1.4 x eps_cfg, and CFG 7.5 amplifies the
     DIFFERENCE of two nearly equal eps 7.5-fold): the kernels must be no worse than 1.25 x an ideal bf16 pipeline,
     i.e. the fp32 oracle with bf16 rounding emulated at every weight / operand / activation store
@@ -101,8 +101,9 @@ def test_config_fullsize_30step(variant, B, scale, kw):
 
 
 def test_unit_scale_absolute_per_step_bound():
-    """Guidance 1.0 (no CFG amplification): latents stay O(1) and the north-star 2e-2 holds as an ABSOLUTE max-abs
-    error on every step of the 30-step schedule (ctrlora r=16, 2 tiles, 64x64 latents)."""
+    """Guidance 1.0 (no CFG amplification of the eps difference): the north-star 2e-2 holds as an ABSOLUTE max-abs error
+    on every step of the 30-step schedule (ctrlora r=16, 2 tiles, 64x64 latents) — measured 8.7e-3 at the first step
+    (|x| = 4.9) and falling from there, although the random-init network drives |x| up to ~70 by the last step."""
     from oracle import ldm_oracle as O
     model = synth.build_model("ctrlora", control_lora_rank=16, with_vae=False).cuda()
     sd = {k: v.float() for k, v in model.state_dict().items()}
@@ -114,7 +115,6 @@ def test_unit_scale_absolute_per_step_bound():
         x_ref, inter = O.ddim_sample(sd, 30, cond, None, 1.0, None, 0.0, xT, scales=scales)
         ts, a, a_prev, _ = O.make_schedule(30)
         steps = _teacher_forced(model, O, ts, a, a_prev, [xT] + inter, ctx, hint, 1.0, "unit scale (guidance 1.0)")
-    assert max(m for _, _, m in steps) < 8.0
     for t, err, mag in steps:
         assert err <= PER_STEP, (t, err, mag)
 
