@@ -343,7 +343,7 @@ struct XAttnSmem {
   static constexpr int ATOMS = (DP + 63) / 64;
   static constexpr int Q_ATOM = ATT_BM * 128, KV_ATOM = XA_NKP * 128;
   static constexpr int Q_BYTES = ATOMS * Q_ATOM, KV_BYTES = ATOMS * KV_ATOM;
-  static constexpr int QS = DP <= 64 ? 4 : (DP <= 80 ? 3 : 2);         // query tiles in flight
+  static constexpr int QS = DP <= 64 ? (NWG >= 4 ? 6 : 4) : (DP <= 80 ? 3 : 2);   // query tiles in flight
   static constexpr int KV_OFF = QS * Q_BYTES;                          // [2 buffers][K | V]
   static constexpr int BAR_OFF = KV_OFF + 4 * KV_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256;
@@ -369,7 +369,7 @@ __device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t* r) {
       : "memory");
 }
 
-template <int DP, int NWG>
+template <int DP, int NWG, int XPOLY>
 __global__ void __launch_bounds__(XAttnSmem<DP, NWG>::THREADS, XAttnSmem<DP, NWG>::CTAS)
 cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group, long long total_tiles) {
   using L = XAttnSmem<DP, NWG>;
@@ -512,62 +512,69 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
       const uint32_t ph = ((i - wg) / NWG) & 1;
       mbar_wait(&s_full[wg], ph);
       tc_fence_after();
-      // ---- pass 1: exact row maximum over the Nk real keys (columns >= Nk hold q . 0 = 0 and are excluded)
-      float mx = -INFINITY;
+      // ---- pass 1: exact row maximum over the Nk real keys (columns >= Nk hold q . 0 = 0 and are excluded).  The three
+      //      TMEM loads are in flight together; the 80 values are only live across the max tree.
+      float mx;
       {
-        float v[32];
-        tmem_ld32(tmem_s, v);
+        float v0[32], v1[32], v2[16];
+        tmem_ld32(tmem_s, v0);
+        tmem_ld32(tmem_s + 32, v1);
+        tmem_ld16(tmem_s + 64, v2);
         tmem_ld_wait();
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, (j < Nk) ? v[j] : -INFINITY);
-        tmem_ld32(tmem_s + 32, v);
-        tmem_ld_wait();
+        for (int j = 0; j < 32; j += 4) {
+          m0 = fmax3(m0, (j < Nk) ? v0[j] : -INFINITY, (j + 1 < Nk) ? v0[j + 1] : -INFINITY);
+          m1 = fmax3(m1, (j + 2 < Nk) ? v0[j + 2] : -INFINITY, (j + 3 < Nk) ? v0[j + 3] : -INFINITY);
+          m2 = fmax3(m2, (32 + j < Nk) ? v1[j] : -INFINITY, (33 + j < Nk) ? v1[j + 1] : -INFINITY);
+          m3 = fmax3(m3, (34 + j < Nk) ? v1[j + 2] : -INFINITY, (35 + j < Nk) ? v1[j + 3] : -INFINITY);
+        }
 #pragma unroll
-        for (int j = 0; j < 32; ++j) mx = fmaxf(mx, (32 + j < Nk) ? v[j] : -INFINITY);
-        float w[16];
-        tmem_ld16(tmem_s + 64, w);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 16; ++j) mx = fmaxf(mx, (64 + j < Nk) ? w[j] : -INFINITY);
+        for (int j = 0; j < 16; j += 4) {
+          m0 = fmax3(m0, (64 + j < Nk) ? v2[j] : -INFINITY, (65 + j < Nk) ? v2[j + 1] : -INFINITY);
+          m1 = fmax3(m1, (66 + j < Nk) ? v2[j + 2] : -INFINITY, (67 + j < Nk) ? v2[j + 3] : -INFINITY);
+        }
+        mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
       }
       const float nm = -mx * c;
-      // ---- pass 2: P = exp2(s c - m c) as packed bf16 pairs written over the S columns already consumed
-      float l = 0.f;
+      const float2 c2 = make_float2(c, c), nm2 = make_float2(nm, nm);
+      // ---- pass 2: P = exp2(s c - m c) as packed bf16 pairs written over the S columns already consumed; the next
+      //      chunk's load is in flight under the exponentials of the current one.  XPOLY of every 8 pairs take the
+      //      FMA-pipe exp2 so the 16/clk MUFU is not the only unit working.
+      float2 ls = make_float2(0.f, 0.f);
+      auto exp_pair = [&](float a, float b, int key, int pair) -> uint32_t {
+        float2 x = ffma2(make_float2(a, b), c2, nm2), e;
+        if ((pair & 7) < XPOLY) {
+          e = exp2_poly2(x);
+        } else {
+          e.x = fast_exp2(x.x);
+          e.y = fast_exp2(x.y);
+        }
+        if (key >= Nk) e.x = 0.f;
+        if (key + 1 >= Nk) e.y = 0.f;
+        ls = fadd2(ls, e);
+        return pack_bf16x2(e.x, e.y);
+      };
       {
-        float v[32];
+        float v0[32], v1[32];
         uint32_t pk[16];
-        tmem_ld32(tmem_s, v);
+        tmem_ld32(tmem_s, v0);
+        tmem_ld32(tmem_s + 32, v1);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          const float e0 = (j < Nk) ? fast_exp2(fmaf(v[j], c, nm)) : 0.f;
-          const float e1 = (j + 1 < Nk) ? fast_exp2(fmaf(v[j + 1], c, nm)) : 0.f;
-          l += e0 + e1;
-          pk[j >> 1] = pack_bf16x2(e0, e1);
-        }
+        for (int j = 0; j < 32; j += 2) pk[j >> 1] = exp_pair(v0[j], v0[j + 1], j, j >> 1);
         tmem_st16u(tmem_s, pk);
-        tmem_ld32(tmem_s + 32, v);
-        tmem_ld_wait();
+        float v2[16];
+        tmem_ld16(tmem_s + 64, v2);   // in flight under the second chunk's exponentials
 #pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          const float e0 = (32 + j < Nk) ? fast_exp2(fmaf(v[j], c, nm)) : 0.f;
-          const float e1 = (33 + j < Nk) ? fast_exp2(fmaf(v[j + 1], c, nm)) : 0.f;
-          l += e0 + e1;
-          pk[j >> 1] = pack_bf16x2(e0, e1);
-        }
+        for (int j = 0; j < 32; j += 2) pk[j >> 1] = exp_pair(v1[j], v1[j + 1], 32 + j, j >> 1);
         tmem_st16u(tmem_s + 16, pk);
-        float w[16];
-        tmem_ld16(tmem_s + 64, w);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; j += 2) {
-          const float e0 = (64 + j < Nk) ? fast_exp2(fmaf(w[j], c, nm)) : 0.f;
-          const float e1 = (65 + j < Nk) ? fast_exp2(fmaf(w[j + 1], c, nm)) : 0.f;
-          l += e0 + e1;
-          pk[j >> 1] = pack_bf16x2(e0, e1);
-        }
+        for (int j = 0; j < 16; j += 2) pk[j >> 1] = exp_pair(v2[j], v2[j + 1], 64 + j, j >> 1);
         tmem_st8(tmem_s + 32, pk);
       }
+      const float l = ls.x + ls.y;
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_ready[wg]);
@@ -580,19 +587,21 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
       bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
       mbar_wait(&o_full[wg], ph);
       tc_fence_after();
+      {
+        float t[DP];
 #pragma unroll
-      for (int c0 = 0; c0 < DP; c0 += 16) {
-        float t[16];
-        tmem_ld16(tmem_o + c0, t);
+        for (int c0 = 0; c0 < DP; c0 += 16) tmem_ld16(tmem_o + c0, t + c0);
         tmem_ld_wait();
         if (qrow < p.Nq) {
-          uint4 u0, u1;
-          u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
-          u0.z = pack_bf16x2(t[4] * inv, t[5] * inv);   u0.w = pack_bf16x2(t[6] * inv, t[7] * inv);
-          u1.x = pack_bf16x2(t[8] * inv, t[9] * inv);   u1.y = pack_bf16x2(t[10] * inv, t[11] * inv);
-          u1.z = pack_bf16x2(t[12] * inv, t[13] * inv); u1.w = pack_bf16x2(t[14] * inv, t[15] * inv);
-          *reinterpret_cast<uint4*>(dst + c0) = u0;
-          *reinterpret_cast<uint4*>(dst + c0 + 8) = u1;
+#pragma unroll
+          for (int c0 = 0; c0 < DP; c0 += 8) {
+            uint4 u;
+            u.x = pack_bf16x2(t[c0 + 0] * inv, t[c0 + 1] * inv);
+            u.y = pack_bf16x2(t[c0 + 2] * inv, t[c0 + 3] * inv);
+            u.z = pack_bf16x2(t[c0 + 4] * inv, t[c0 + 5] * inv);
+            u.w = pack_bf16x2(t[c0 + 6] * inv, t[c0 + 7] * inv);
+            *reinterpret_cast<uint4*>(dst + c0) = u;
+          }
         }
       }
       // O(i) is out of TMEM before this warpgroup's next p_ready arrival, which is what lets the issuer start P V(i + NWG)
@@ -609,10 +618,10 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
   }
 }
 
-template <int DP, int NWG>
+template <int DP, int NWG, int XPOLY>
 static int launch_cross_attention(const AttnParams& p, int B, cudaStream_t st) {
   using L = XAttnSmem<DP, NWG>;
-  auto kfn = cross_attention_kernel<DP, NWG>;
+  auto kfn = cross_attention_kernel<DP, NWG, XPOLY>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
   const int tiles_per_group = (p.Nq + ATT_BM - 1) / ATT_BM;
   const long long total = (long long)tiles_per_group * p.heads * B;
@@ -622,7 +631,7 @@ static int launch_cross_attention(const AttnParams& p, int B, cudaStream_t st) {
   if (ctas > want) ctas = want;
   kfn<<<dim3((unsigned)ctas), L::THREADS, L::TOTAL, st>>>(p, tiles_per_group, total);
   TOPO_CUDA(cudaGetLastError());
-  note_kernel("cross_attention_kernel<%d, %d>", DP, NWG);
+  note_kernel("cross_attention_kernel<%d, %d, %d>", DP, NWG, XPOLY);
   return 0;
 }
 
@@ -709,9 +718,20 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
     if (rc) return rc;
     rc = make_tmap(&p.tm_v, v, 3, dims, strv, bx, 128);
     if (rc) return rc;
-    if (dp == 48) return launch_cross_attention<48, 2>(p, B, st);
-    if (dp == 80) return launch_cross_attention<80, 3>(p, B, st);
-    return launch_cross_attention<160, 2>(p, B, st);
+    // TOPO_XATTN_CFG = <warpgroups><poly eighths>, e.g. 43 = 4 warpgroups (one CTA per SM), 3 of 8 pairs on the FMA pipe (A/B runs)
+    static const int cfg = [] { const char* e = getenv("TOPO_XATTN_CFG"); return e ? atoi(e) : 0; }();
+    if (dp == 48) {
+      switch (cfg) {
+        case 20: return launch_cross_attention<48, 2, 0>(p, B, st);
+        case 22: return launch_cross_attention<48, 2, 2>(p, B, st);
+        case 40: return launch_cross_attention<48, 4, 0>(p, B, st);
+        case 42: return launch_cross_attention<48, 4, 2>(p, B, st);
+        case 43: return launch_cross_attention<48, 4, 3>(p, B, st);
+        default: return launch_cross_attention<48, 2, 3>(p, B, st);
+      }
+    }
+    if (dp == 80) return cfg == 20 || cfg == 40 ? launch_cross_attention<80, 3, 0>(p, B, st) : launch_cross_attention<80, 3, 3>(p, B, st);
+    return cfg == 20 || cfg == 40 ? launch_cross_attention<160, 2, 0>(p, B, st) : launch_cross_attention<160, 2, 3>(p, B, st);
   }
   const int np = attn_npoly(dp);
   const int ns = attn_streams(dp, Nq);
