@@ -216,3 +216,31 @@ def test_sample_log_cfg_free():
     print(f"[parity] sample_log (CFG-free, 10 steps): cos={cos:.6f} rel_max={err:.3e}")
     assert torch.equal(inter["x_inter"][0], xT) and z.shape == (B, 4, lat, lat)
     assert cos >= 0.999 and err <= 5e-2
+
+
+def test_control_lora_vs_reference_golden():
+    """The CUDA path against outputs of the REFERENCE's own attention_lora.py classes (tests/golden/control_lora.pt,
+    generated by tests/golden/make_golden.py): ControlLoRA encoder, and CrossAttention_LoRA_Control.forward with and
+    without control states (bf16 kernels vs the reference's fp32: 2e-2 of the output range)."""
+    import os
+    from topo_b200 import lora
+    d = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "control_lora.pt"))
+    enc = lora.ControlLoRA()
+    enc.load_state_dict(d["enc_sd"])
+    with torch.no_grad():
+        y = enc.cuda()(d["enc_x"].cuda())
+    e_enc = _rel(y, d["enc_y"].cuda())
+    attn = lora.CrossAttention_LoRA_Control(query_dim=128, context_dim=192, heads=2, dim_head=64, lora_rank=4, control_rank=6)
+    attn.load_state_dict(d["attn_sd"])
+    attn = attn.cuda()
+    x, ctx, cs = d["x"].cuda(), d["ctx"].cuda(), d["cs"].cuda()
+    with torch.no_grad():
+        y0 = attn(x, ctx)
+        attn.inject_control_states(cs)
+        y1 = attn(x, ctx, scale=d["scale"])
+        attn.inject_control_states(cs[:, :, :2])
+        yb = attn(x, ctx, scale=d["scale"])
+    e0, e1 = _rel(y0, d["y_none"].cuda()), _rel(y1, d["y_ctrl"].cuda())
+    print(f"[parity] vs reference attention_lora.py outputs: ControlLoRA rel={e_enc:.3e}; attention rel={e0:.3e}; "
+          f"attention + control rel={e1:.3e}")
+    assert e_enc <= 2e-2 and e0 <= 2e-2 and e1 <= 2e-2 and torch.equal(yb, y0)

@@ -80,3 +80,56 @@ def test_oracle_tiny_model_runs_and_is_deterministic():
     assert len(inter) == 2 and float(img.std()) > 1e-3
     u8 = O.tiles_to_uint8(img)
     assert u8.dtype == np.uint8 and u8.shape == (1, 64, 64, 3)
+
+
+def _golden_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(G, "make_golden.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_control_lora_matches_reference_attention_lora():
+    """oracle.control_lora_encoder / lora_control_attention == the reference's own ControlLoRA and
+    CrossAttention_LoRA_Control (LoRA_modified/attention_lora.py:35-101) on its own outputs (fp32, 1e-5)."""
+    d = torch.load(os.path.join(G, "control_lora.pt"))
+    y = O.control_lora_encoder({"e." + k: v for k, v in d["enc_sd"].items()}, "e", d["enc_x"])
+    assert y.shape == d["enc_y"].shape == (2, 256, 16, 16) and torch.allclose(y, d["enc_y"], atol=1e-5, rtol=1e-5)
+    sd = {"a." + k: v for k, v in d["attn_sd"].items()}
+    assert d["scaling"] == 2.0 and d["y_bad_equals_none"]
+    y0 = O.lora_control_attention(sd, "a", d["x"], d["ctx"], 2, None)
+    y1 = O.lora_control_attention(sd, "a", d["x"], d["ctx"], 2, d["cs"], d["scale"])
+    yb = O.lora_control_attention(sd, "a", d["x"], d["ctx"], 2, d["cs"][:, :, :2], d["scale"])
+    assert torch.allclose(y0, d["y_none"], atol=1e-5, rtol=1e-5) and torch.allclose(y1, d["y_ctrl"], atol=1e-5, rtol=1e-5)
+    assert torch.allclose(y1 - y0, d["ctrl"], atol=1e-5) and torch.equal(yb, y0)
+    assert float((d["y_ctrl"] - d["y_none"]).abs().max()) > 0.05          # the control term is not negligible in the fixture
+
+
+def test_drivers_match_reference_vis_metrics(monkeypatch):
+    """This repo's ``validate_step`` / ``sample_preview`` against outputs of the REFERENCE's own functions
+    (TextEncoder_Finetuning/vis_metrics.py:73-116, 407-452) run on the same deterministic mock model and recording
+    sampler (tests/golden/make_golden.py): identical eps-MSE, identical call sequence, identical sampler arguments
+    (zeros uc, shared hint object, S, shape, scale, eta, x_T=None after manual_seed(seed)), identical decoded preview."""
+    mg = _golden_module()
+    d = torch.load(os.path.join(G, "drivers.pt"), weights_only=False)
+    from topo_b200 import sampling
+    batch, model = mg.driver_batch(), mg.MockLDM()
+    torch.manual_seed(5)
+    val = sampling.validate_step(model, mg.MockEnc(), batch, "cpu", iters=3)
+    assert val == d["validate"] and model.calls == d["validate_calls"]
+    val_fixed = sampling.validate_step(model, mg.MockEnc(), batch, "cpu", iters=2, fixed_t=d["fixed_t"], fixed_noise=d["fixed_noise"])
+    assert val_fixed == d["validate_fixed"]
+    monkeypatch.setattr(sampling, "DDIMSampler", mg.RecordingSampler)
+    pred = sampling.sample_preview(model, mg.MockEnc(), batch, "cpu", steps=12, scale=6.5, eta=0.0, seed=4321)
+    assert torch.equal(pred, d["preview"]) and float(pred.max()) == 1.0 and float(pred.min()) == -1.0
+    got, want = mg.RecordingSampler.last, d["sampler_kwargs"]
+    assert sorted(got) == sorted(want)
+    for k in want:
+        if isinstance(want[k], dict):
+            assert sorted(got[k]) == sorted(want[k])
+            for n in want[k]:
+                assert all(torch.equal(a, b) for a, b in zip(got[k][n], want[k][n])), (k, n)
+        else:
+            assert got[k] == want[k], k
+    assert got["same_hint_object"] and not bool(got["unconditional_conditioning"]["c_crossattn"][0].any())
