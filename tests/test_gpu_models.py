@@ -174,3 +174,40 @@ def test_control_lora_pyramid():
         print(f"[parity] ControlLoRA level {i}: cosine={cos:.6f}")
         assert cos >= 0.999
         assert_close(a, b, 4e-2, f"ControlLoRA control map {i}")
+
+
+def test_processors_and_pyramid_vs_reference_golden():
+    """The CUDA path against outputs of the REFERENCE's own LoRA_modified/models.py (tests/golden/models_ref.pt, generated
+    by tests/golden/make_golden_models.py): nine processor configurations (post_add, skip flags, control v1 with
+    concat_hidden / batch repeat / pre+post stacks, V2) and the ControlLoRA pyramid."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_oracle_golden import G, _build_proc
+    from topo_b200 import models as M
+    d = torch.load(os.path.join(G, "models_ref.pt"), weights_only=False)
+    dims = d["dims"]
+    Cg, ctx = dims["C"], dims["ctx"]
+    for name, rec in d["cases"].items():
+        attn = M.CrossAttention(Cg, ctx if rec["cross"] else None, dims["heads"], dims["d"])
+        attn.load_state_dict(d["attn_cross" if rec["cross"] else "attn_self"])
+        attn = attn.cuda()
+        proc = _build_proc(M, rec, Cg, ctx).cuda()
+        if "control" in rec:
+            proc.inject_control_states(rec["control"].clone().cuda())
+        for extra in list(getattr(proc, "pre_loras", [])) + list(getattr(proc, "post_loras", [])):
+            extra.cuda()
+        attn.set_processor(proc)
+        got = attn(d["hidden"].cuda(), encoder_hidden_states=d["enc"].cuda() if rec["cross"] else None, scale=rec["scale"])
+        ref = rec["out"].cuda()
+        cos = torch.nn.functional.cosine_similarity(got.flatten().float(), ref.flatten(), dim=0).item()
+        print(f"[parity] vs reference models.py {name}: cosine={cos:.6f}")
+        assert cos >= 0.999
+        assert_close(got, ref, 2e-2, f"reference golden {name}")
+    p = d["pyramid"]
+    pyr = M.ControlLoRA(**p["kw"])
+    pyr.load_state_dict(p["sd"])
+    maps = pyr.cuda()(p["x"].cuda(), return_dict=False)
+    assert pyr(p["x"].cuda()) is None                      # the reference's forward returns None with return_dict=True
+    for i, (got, want) in enumerate(zip(maps, p["maps"])):
+        assert_close(got, want.cuda(), 4e-2, f"reference golden pyramid map {i}")

@@ -133,3 +133,51 @@ def test_drivers_match_reference_vis_metrics(monkeypatch):
         else:
             assert got[k] == want[k], k
     assert got["same_hint_object"] and not bool(got["unconditional_conditioning"]["c_crossattn"][0].any())
+
+
+def _build_proc(M, rec, C, ctx):
+    """This repo's processor object for one golden case, loaded with the reference's state dict."""
+    cls = getattr(M, rec["cls"])
+    proc = cls(C, cross_attention_dim=ctx if rec["cross"] else None, **rec["kw"])
+    proc.load_state_dict(rec["sd"])
+    if "control" in rec:
+        proc.inject_control_states(rec["control"].clone())
+    if "pre_sd" in rec:
+        pre = M.LoRACrossAttnProcessor(C, ctx, rank=4)
+        pre.load_state_dict(rec["pre_sd"])
+        post = M.LoRACrossAttnProcessor(C, ctx, rank=8, post_add=True)
+        post.load_state_dict(rec["post_sd"])
+        proc.inject_pre_lora(pre)
+        proc.inject_post_lora(post)
+    return proc
+
+
+def test_models_oracle_matches_reference_models_py():
+    """oracle/models_oracle.py == the reference's own LoRA_modified/models.py (processor algebra :70-431 and the
+    ControlLoRA pyramid :434-833) on outputs generated by running that file (tests/golden/make_golden_models.py; the
+    diffusers primitives it imports are stand-ins restating diffusers 0.12, everything on top is the reference's code).
+    The same state dicts load into this repo's classes: constructor signatures and key names are the reference's."""
+    from oracle import models_oracle as MO
+    from topo_b200 import models as M
+    d = torch.load(os.path.join(G, "models_ref.pt"), weights_only=False)
+    dims = d["dims"]
+    C, ctx = dims["C"], dims["ctx"]
+    attns = {}
+    for cross in (False, True):
+        a = M.CrossAttention(C, ctx if cross else None, dims["heads"], dims["d"])
+        a.load_state_dict(d["attn_cross" if cross else "attn_self"])
+        attns[cross] = a
+    assert len(d["cases"]) == 9
+    for name, rec in d["cases"].items():
+        proc = _build_proc(M, rec, C, ctx)
+        out = MO.processor_call(attns[rec["cross"]], proc, d["hidden"], d["enc"] if rec["cross"] else None, rec["scale"])
+        err = (out - rec["out"]).abs().max().item()
+        assert out.shape == rec["out"].shape and err <= 2e-5 * max(1.0, rec["out"].abs().max().item()), (name, err)
+    p = d["pyramid"]
+    pyr = M.ControlLoRA(**p["kw"])
+    missing = pyr.load_state_dict(p["sd"], strict=True)
+    maps = MO.control_lora_forward(pyr, p["x"], inject=True)
+    assert p["return_dict_true_is_none"] and len(maps) == 4
+    for got, want in zip(maps, p["maps"]):
+        assert got.shape == want.shape and torch.allclose(got, want, atol=2e-5, rtol=1e-4)
+    assert [tuple(l[0].control_states.shape) for l in pyr.lora_layers] == [tuple(s) for s in p["injected_shapes"]]
