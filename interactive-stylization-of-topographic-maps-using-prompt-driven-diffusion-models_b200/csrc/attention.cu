@@ -31,6 +31,7 @@ constexpr int ATT_BN = 64;   // keys per block
 
 struct alignas(64) AttnParams {
   CUtensorMap tm_q, tm_k, tm_v;  // 3-D (cols, rows, batch); box (64, 128, 1) for Q, (64, 64, 1) for K/V; SW128
+  CUtensorMap tm_o;              // cross_attention_kernel only: output, box (dp, 128, 1), no swizzle (TMA store)
   bf16* o;
   const int* kv_len;             // optional [B]: keys >= kv_len[b] are masked (right-padded prompts); nullptr = all Nk
   int Nq, Nk, heads, ldo;
@@ -337,21 +338,24 @@ attention_kernel(const __grid_constant__ AttnParams p) {
 // warps: 0 = TMA producer, 1 = MMA issuer + TMEM owner, 2.. = NWG x 4 softmax/epilogue warps.
 constexpr int XA_NKP = 80;  // keys per tile, padded: UMMA N (multiple of 16) and P's K extent
 
-template <int DP, int NWG>
+template <int DP, int NWG, bool TMAST>
 struct XAttnSmem {
   static constexpr int THREADS = 32 * (2 + 4 * NWG);
   static constexpr int ATOMS = (DP + 63) / 64;
   static constexpr int Q_ATOM = ATT_BM * 128, KV_ATOM = XA_NKP * 128;
   static constexpr int Q_BYTES = ATOMS * Q_ATOM, KV_BYTES = ATOMS * KV_ATOM;
-  static constexpr int QS = DP <= 64 ? (NWG >= 4 ? 6 : 4) : (DP <= 80 ? 3 : 2);   // query tiles in flight
+  static constexpr int QS = DP <= 64 ? (TMAST ? 3 : 4) : (DP <= 80 ? 3 : 2);   // query tiles in flight
   static constexpr int KV_OFF = QS * Q_BYTES;                          // [2 buffers][K | V]
-  static constexpr int BAR_OFF = KV_OFF + 4 * KV_BYTES;
+  static constexpr int OST_OFF = KV_OFF + 4 * KV_BYTES;                // TMAST: one dense [128][DP] bf16 output tile per warpgroup
+  static constexpr int OST_BYTES = TMAST ? ATT_BM * DP * 2 : 0;
+  static constexpr int BAR_OFF = OST_OFF + NWG * OST_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256;
   static constexpr uint32_t O_COL = XA_NKP;                            // slot: S fp32 [0,80) (P bf16x2 over [0,40)) | O fp32 [80, 80+DP)
   static constexpr uint32_t SLOT_COLS = O_COL + ((DP + 15) / 16) * 16;
   static constexpr uint32_t TMEM_COLS = NWG * SLOT_COLS <= 256 ? 256 : 512;
   static constexpr int CTAS = 512 / TMEM_COLS;
   static_assert(NWG * SLOT_COLS <= 512, "TMEM");
+  static_assert(NWG <= 3 || !TMAST, "one named barrier per warpgroup (ids 1..3)");
   static_assert(CTAS * (TOTAL + 1024) <= 228 * 1024, "smem");
 };
 
@@ -368,11 +372,21 @@ __device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t* r) {
       "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
 }
+// TMA store of a dense shared-memory box (no swizzle) to a 3-D tensor; rows / columns outside the tensor are clipped
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
-template <int DP, int NWG, int XPOLY>
-__global__ void __launch_bounds__(XAttnSmem<DP, NWG>::THREADS, XAttnSmem<DP, NWG>::CTAS)
+template <int DP, int NWG, bool TMAST>
+__global__ void __launch_bounds__(XAttnSmem<DP, NWG, TMAST>::THREADS, XAttnSmem<DP, NWG, TMAST>::CTAS)
 cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group, long long total_tiles) {
-  using L = XAttnSmem<DP, NWG>;
+  using L = XAttnSmem<DP, NWG, TMAST>;
   constexpr int ATOMS = L::ATOMS, QS = L::QS;
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -400,6 +414,7 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
     tma_prefetch_desc(&p.tm_q);
     tma_prefetch_desc(&p.tm_k);
     tma_prefetch_desc(&p.tm_v);
+    if (TMAST) tma_prefetch_desc(&p.tm_o);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&kv_full[i], 1);
       mbar_init(&kv_empty[i], 1);
@@ -508,105 +523,150 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
     const uint32_t tmem_o = tmem_s + L::O_COL;
     const float c = p.scale_log2e;
     const int Nk = p.Nk;
+    const bool full64 = Nk >= 64;   // the 77-token prompt: only the last 16-column chunk has columns to mask
+    uint8_t* o_stage = smem + L::OST_OFF + wg * L::OST_BYTES;
+    const bool store_leader = (warp - 2) % 4 == 0 && lane == 0;
     for (int i = wg; i < n; i += NWG) {
       const uint32_t ph = ((i - wg) / NWG) & 1;
       mbar_wait(&s_full[wg], ph);
       tc_fence_after();
-      // ---- pass 1: exact row maximum over the Nk real keys (columns >= Nk hold q . 0 = 0 and are excluded).  The three
-      //      TMEM loads are in flight together; the 80 values are only live across the max tree.
+      // ---- pass 1: exact row maximum over the Nk real keys (columns >= Nk hold q . 0 = 0 and are excluded)
       float mx;
       {
-        float v0[32], v1[32], v2[16];
-        tmem_ld32(tmem_s, v0);
-        tmem_ld32(tmem_s + 32, v1);
-        tmem_ld16(tmem_s + 64, v2);
+        float v[32];
+        float m0 = -INFINITY, m1 = -INFINITY;
+        tmem_ld32(tmem_s, v);
         tmem_ld_wait();
-        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+        if (full64) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          m0 = fmax3(m0, (j < Nk) ? v0[j] : -INFINITY, (j + 1 < Nk) ? v0[j + 1] : -INFINITY);
-          m1 = fmax3(m1, (j + 2 < Nk) ? v0[j + 2] : -INFINITY, (j + 3 < Nk) ? v0[j + 3] : -INFINITY);
-          m2 = fmax3(m2, (32 + j < Nk) ? v1[j] : -INFINITY, (33 + j < Nk) ? v1[j + 1] : -INFINITY);
-          m3 = fmax3(m3, (34 + j < Nk) ? v1[j + 2] : -INFINITY, (35 + j < Nk) ? v1[j + 3] : -INFINITY);
-        }
+          for (int j = 0; j < 32; j += 4) {
+            m0 = fmax3(m0, v[j], v[j + 1]);
+            m1 = fmax3(m1, v[j + 2], v[j + 3]);
+          }
+        } else {
 #pragma unroll
-        for (int j = 0; j < 16; j += 4) {
-          m0 = fmax3(m0, (64 + j < Nk) ? v2[j] : -INFINITY, (65 + j < Nk) ? v2[j + 1] : -INFINITY);
-          m1 = fmax3(m1, (66 + j < Nk) ? v2[j + 2] : -INFINITY, (67 + j < Nk) ? v2[j + 3] : -INFINITY);
+          for (int j = 0; j < 32; ++j) m0 = fmaxf(m0, (j < Nk) ? v[j] : -INFINITY);
         }
-        mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+        tmem_ld32(tmem_s + 32, v);
+        tmem_ld_wait();
+        if (full64) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            m0 = fmax3(m0, v[j], v[j + 1]);
+            m1 = fmax3(m1, v[j + 2], v[j + 3]);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) m0 = fmaxf(m0, (32 + j < Nk) ? v[j] : -INFINITY);
+        }
+        float w[16];
+        tmem_ld16(tmem_s + 64, w);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) m1 = fmaxf(m1, (64 + j < Nk) ? w[j] : -INFINITY);
+        mx = fmaxf(m0, m1);
       }
       const float nm = -mx * c;
       const float2 c2 = make_float2(c, c), nm2 = make_float2(nm, nm);
-      // ---- pass 2: P = exp2(s c - m c) as packed bf16 pairs written over the S columns already consumed; the next
-      //      chunk's load is in flight under the exponentials of the current one.  XPOLY of every 8 pairs take the
-      //      FMA-pipe exp2 so the 16/clk MUFU is not the only unit working.
+      // ---- pass 2: P = exp2(s c - m c) as packed bf16 pairs written over the S columns already consumed
       float2 ls = make_float2(0.f, 0.f);
-      auto exp_pair = [&](float a, float b, int key, int pair) -> uint32_t {
-        float2 x = ffma2(make_float2(a, b), c2, nm2), e;
-        if ((pair & 7) < XPOLY) {
-          e = exp2_poly2(x);
-        } else {
-          e.x = fast_exp2(x.x);
-          e.y = fast_exp2(x.y);
-        }
-        if (key >= Nk) e.x = 0.f;
-        if (key + 1 >= Nk) e.y = 0.f;
-        ls = fadd2(ls, e);
-        return pack_bf16x2(e.x, e.y);
-      };
       {
-        float v0[32], v1[32];
+        float v[32];
         uint32_t pk[16];
-        tmem_ld32(tmem_s, v0);
-        tmem_ld32(tmem_s + 32, v1);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          tmem_ld32(tmem_s + 32 * h, v);
+          tmem_ld_wait();
+          if (full64) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float2 x = ffma2(make_float2(v[j], v[j + 1]), c2, nm2);
+              const float2 e = make_float2(fast_exp2(x.x), fast_exp2(x.y));
+              ls = fadd2(ls, e);
+              pk[j >> 1] = pack_bf16x2(e.x, e.y);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              const float e0 = (32 * h + j < Nk) ? fast_exp2(fmaf(v[j], c, nm)) : 0.f;
+              const float e1 = (32 * h + j + 1 < Nk) ? fast_exp2(fmaf(v[j + 1], c, nm)) : 0.f;
+              ls = fadd2(ls, make_float2(e0, e1));
+              pk[j >> 1] = pack_bf16x2(e0, e1);
+            }
+          }
+          tmem_st16u(tmem_s + 16 * h, pk);
+        }
+        float w[16];
+        tmem_ld16(tmem_s + 64, w);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; j += 2) pk[j >> 1] = exp_pair(v0[j], v0[j + 1], j, j >> 1);
-        tmem_st16u(tmem_s, pk);
-        float v2[16];
-        tmem_ld16(tmem_s + 64, v2);   // in flight under the second chunk's exponentials
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) pk[j >> 1] = exp_pair(v1[j], v1[j + 1], 32 + j, j >> 1);
-        tmem_st16u(tmem_s + 16, pk);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 16; j += 2) pk[j >> 1] = exp_pair(v2[j], v2[j + 1], 64 + j, j >> 1);
+        for (int j = 0; j < 16; j += 2) {
+          const float e0 = (64 + j < Nk) ? fast_exp2(fmaf(w[j], c, nm)) : 0.f;
+          const float e1 = (65 + j < Nk) ? fast_exp2(fmaf(w[j + 1], c, nm)) : 0.f;
+          ls = fadd2(ls, make_float2(e0, e1));
+          pk[j >> 1] = pack_bf16x2(e0, e1);
+        }
         tmem_st8(tmem_s + 32, pk);
       }
-      const float l = ls.x + ls.y;
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_ready[wg]);
-      // ---- epilogue: O / l -> bf16 -> global (row per thread, 2 x 16 bytes per 16 columns)
-      const float inv = 1.0f / l;
+      // ---- epilogue: O / l -> bf16 -> global
+      const float inv = 1.0f / (ls.x + ls.y);
       const long long g = g0 + i;
       const int grp = (int)(g / tiles_per_group), tile = (int)(g - (long long)grp * tiles_per_group);
       const int b = grp / p.heads, col0 = (grp - b * p.heads) * DP;
-      const int qrow = tile * ATT_BM + row;
-      bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
+      if (TMAST) {
+        // the TMA store of this warpgroup's previous tile must have finished READING the staging tile
+        if (store_leader) tma_store_wait_read();
+        named_bar_sync(1 + wg, 128);
+      }
       mbar_wait(&o_full[wg], ph);
       tc_fence_after();
-      {
-        float t[DP];
+      if (TMAST) {
+        // row per thread into the dense [128][DP] staging tile, then ONE bulk tensor store per tile: no per-thread global
+        // stores (each used to touch 32 different 128-byte lines per instruction), rows past Nq are clipped by the TMA
+        uint8_t* srow = o_stage + row * (DP * 2);
 #pragma unroll
-        for (int c0 = 0; c0 < DP; c0 += 16) tmem_ld16(tmem_o + c0, t + c0);
-        tmem_ld_wait();
-        if (qrow < p.Nq) {
+        for (int c0 = 0; c0 < DP; c0 += 16) {
+          float t[16];
+          tmem_ld16(tmem_o + c0, t);
+          tmem_ld_wait();
+          uint4 u0, u1;
+          u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
+          u0.z = pack_bf16x2(t[4] * inv, t[5] * inv);   u0.w = pack_bf16x2(t[6] * inv, t[7] * inv);
+          u1.x = pack_bf16x2(t[8] * inv, t[9] * inv);   u1.y = pack_bf16x2(t[10] * inv, t[11] * inv);
+          u1.z = pack_bf16x2(t[12] * inv, t[13] * inv); u1.w = pack_bf16x2(t[14] * inv, t[15] * inv);
+          *reinterpret_cast<uint4*>(srow + c0 * 2) = u0;
+          *reinterpret_cast<uint4*>(srow + c0 * 2 + 16) = u1;
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_sync(1 + wg, 128);
+        if (store_leader) tma_store_3d(&p.tm_o, o_stage, col0, tile * ATT_BM, b);
+      } else {
+        const int qrow = tile * ATT_BM + row;
+        bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
 #pragma unroll
-          for (int c0 = 0; c0 < DP; c0 += 8) {
-            uint4 u;
-            u.x = pack_bf16x2(t[c0 + 0] * inv, t[c0 + 1] * inv);
-            u.y = pack_bf16x2(t[c0 + 2] * inv, t[c0 + 3] * inv);
-            u.z = pack_bf16x2(t[c0 + 4] * inv, t[c0 + 5] * inv);
-            u.w = pack_bf16x2(t[c0 + 6] * inv, t[c0 + 7] * inv);
-            *reinterpret_cast<uint4*>(dst + c0) = u;
+        for (int c0 = 0; c0 < DP; c0 += 16) {
+          float t[16];
+          tmem_ld16(tmem_o + c0, t);
+          tmem_ld_wait();
+          if (qrow < p.Nq) {
+            uint4 u0, u1;
+            u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
+            u0.z = pack_bf16x2(t[4] * inv, t[5] * inv);   u0.w = pack_bf16x2(t[6] * inv, t[7] * inv);
+            u1.x = pack_bf16x2(t[8] * inv, t[9] * inv);   u1.y = pack_bf16x2(t[10] * inv, t[11] * inv);
+            u1.z = pack_bf16x2(t[12] * inv, t[13] * inv); u1.w = pack_bf16x2(t[14] * inv, t[15] * inv);
+            *reinterpret_cast<uint4*>(dst + c0) = u0;
+            *reinterpret_cast<uint4*>(dst + c0 + 8) = u1;
           }
         }
+        tc_fence_before();
       }
       // O(i) is out of TMEM before this warpgroup's next p_ready arrival, which is what lets the issuer start P V(i + NWG)
-      tc_fence_before();
     }
+    if (TMAST && store_leader) tma_store_wait_all();
     __syncwarp();
   }
 
@@ -618,10 +678,10 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
   }
 }
 
-template <int DP, int NWG, int XPOLY>
+template <int DP, int NWG, bool TMAST>
 static int launch_cross_attention(const AttnParams& p, int B, cudaStream_t st) {
-  using L = XAttnSmem<DP, NWG>;
-  auto kfn = cross_attention_kernel<DP, NWG, XPOLY>;
+  using L = XAttnSmem<DP, NWG, TMAST>;
+  auto kfn = cross_attention_kernel<DP, NWG, TMAST>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
   const int tiles_per_group = (p.Nq + ATT_BM - 1) / ATT_BM;
   const long long total = (long long)tiles_per_group * p.heads * B;
@@ -631,7 +691,7 @@ static int launch_cross_attention(const AttnParams& p, int B, cudaStream_t st) {
   if (ctas > want) ctas = want;
   kfn<<<dim3((unsigned)ctas), L::THREADS, L::TOTAL, st>>>(p, tiles_per_group, total);
   TOPO_CUDA(cudaGetLastError());
-  note_kernel("cross_attention_kernel<%d, %d, %d>", DP, NWG, XPOLY);
+  note_kernel("cross_attention_kernel<%d, %d, %d>", DP, NWG, (int)TMAST);
   return 0;
 }
 
@@ -718,20 +778,21 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
     if (rc) return rc;
     rc = make_tmap(&p.tm_v, v, 3, dims, strv, bx, 128);
     if (rc) return rc;
-    // TOPO_XATTN_CFG = <warpgroups><poly eighths>, e.g. 43 = 4 warpgroups (one CTA per SM), 3 of 8 pairs on the FMA pipe (A/B runs)
-    static const int cfg = [] { const char* e = getenv("TOPO_XATTN_CFG"); return e ? atoi(e) : 0; }();
-    if (dp == 48) {
-      switch (cfg) {
-        case 20: return launch_cross_attention<48, 2, 0>(p, B, st);
-        case 22: return launch_cross_attention<48, 2, 2>(p, B, st);
-        case 40: return launch_cross_attention<48, 4, 0>(p, B, st);
-        case 42: return launch_cross_attention<48, 4, 2>(p, B, st);
-        case 43: return launch_cross_attention<48, 4, 3>(p, B, st);
-        default: return launch_cross_attention<48, 2, 3>(p, B, st);
-      }
+    // the output goes out through ONE TMA store per tile (dense [128][dp] box, clipped at Nq) where the staging tile fits;
+    // TOPO_XATTN_TMAST=0 keeps the per-thread row stores (A/B runs)
+    static const bool tmast = [] { const char* e = getenv("TOPO_XATTN_TMAST"); return !(e && e[0] == '0'); }();
+    if (tmast && dp != 160) {
+      uint64_t od[3] = {cols, (uint64_t)Nq, (uint64_t)B};
+      uint64_t os[2] = {(uint64_t)ldo * 2, (uint64_t)ldo * 2 * Nq};
+      uint32_t ob[3] = {(uint32_t)dp, (uint32_t)ATT_BM, 1};
+      rc = make_tmap(&p.tm_o, o, 3, od, os, ob, 0);
+      if (rc) return rc;
+      if (dp == 48) return launch_cross_attention<48, 2, true>(p, B, st);
+      return launch_cross_attention<80, 2, true>(p, B, st);
     }
-    if (dp == 80) return cfg == 20 || cfg == 40 ? launch_cross_attention<80, 3, 0>(p, B, st) : launch_cross_attention<80, 3, 3>(p, B, st);
-    return cfg == 20 || cfg == 40 ? launch_cross_attention<160, 2, 0>(p, B, st) : launch_cross_attention<160, 2, 3>(p, B, st);
+    if (dp == 48) return launch_cross_attention<48, 2, false>(p, B, st);
+    if (dp == 80) return launch_cross_attention<80, 3, false>(p, B, st);
+    return launch_cross_attention<160, 2, false>(p, B, st);
   }
   const int np = attn_npoly(dp);
   const int ns = attn_streams(dp, Nq);

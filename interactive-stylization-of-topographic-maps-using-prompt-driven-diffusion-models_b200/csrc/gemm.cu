@@ -524,12 +524,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32);
           const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32);
 #pragma unroll
-          for (int u = 0; u < 8; ++u) {
+          const float2 al2 = make_float2(alpha, alpha);
+          for (int u = 0; u < 8; ++u) {   // packed FP32x2 throughout: the GEGLU epilogue is issue bound (profiles/r01e_geglu.md)
             const float4 a4 = ba[u], g4 = bg[u];
-            v[4 * u + 0] = (v[4 * u + 0] + a4.x) * gelu_erf_f(g[4 * u + 0] + g4.x) * alpha;
-            v[4 * u + 1] = (v[4 * u + 1] + a4.y) * gelu_erf_f(g[4 * u + 1] + g4.y) * alpha;
-            v[4 * u + 2] = (v[4 * u + 2] + a4.z) * gelu_erf_f(g[4 * u + 2] + g4.z) * alpha;
-            v[4 * u + 3] = (v[4 * u + 3] + a4.w) * gelu_erf_f(g[4 * u + 3] + g4.w) * alpha;
+            const float2 ge0 = gelu_erf2(fadd2(make_float2(g[4 * u + 0], g[4 * u + 1]), make_float2(g4.x, g4.y)));
+            const float2 ge1 = gelu_erf2(fadd2(make_float2(g[4 * u + 2], g[4 * u + 3]), make_float2(g4.z, g4.w)));
+            const float2 o0 = fmul2(fmul2(fadd2(make_float2(v[4 * u + 0], v[4 * u + 1]), make_float2(a4.x, a4.y)), ge0), al2);
+            const float2 o1 = fmul2(fmul2(fadd2(make_float2(v[4 * u + 2], v[4 * u + 3]), make_float2(a4.z, a4.w)), ge1), al2);
+            v[4 * u + 0] = o0.x; v[4 * u + 1] = o0.y; v[4 * u + 2] = o1.x; v[4 * u + 3] = o1.y;
           }
         } else {
           tmem_ld_wait32(v);
@@ -801,6 +803,8 @@ static int fill_seg(GemmSegDev& d, const topo_linear_t& s, int K, int taps, int 
   TOPO_CHECK(s.W && s.out, TOPO_E_INVAL, "topo_linear_t: W/out must be non-null");
   TOPO_CHECK(s.r_pad == 0 || s.r_pad == 16 || s.r_pad == 32, TOPO_E_INVAL, "r_pad must be 0, 16 or 32 (got %d)", s.r_pad);
   TOPO_CHECK(s.act != TOPO_ACT_GEGLU || (s.N % BN == 0), TOPO_E_INVAL, "GEGLU needs N %% %d == 0", BN);
+  TOPO_CHECK(s.act != TOPO_ACT_GEGLU || s.r_pad == 0, TOPO_E_INVAL, "GEGLU epilogue with a LoRA branch is not implemented "
+             "(the value|gate interleave granularity is tied to the non-LoRA tile width)");
   uint64_t dims[2] = {(uint64_t)taps * K, (uint64_t)s.N};
   uint64_t strides[1] = {(uint64_t)taps * K * 2};
   uint32_t box[2] = {BK, (uint32_t)(box_n ? box_n : BN)};  // box_n = BN / 2: each CTA of a pair loads half of the W rows
@@ -852,6 +856,14 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   // measured: the short-K projections gain 8 % (98 -> 90 us at K = 320 / 384); K = 1280 and the 3x3 convs do not
   // (convs lose 5 %), so only K < 1024 GEMMs take the 160-wide tile
   if (use_bn160(segs[0].N, segs[0].r_pad, n_seg, segs[0].act) && K < 1024 && (M + BM - 1) / BM >= sm_count()) BN = 160;
+  // fused q/k/v of the 64x64 level (3 x 384 columns): two 192-wide tiles per segment instead of three 128-wide ones, i.e.
+  // a third fewer passes over x per row tile (TOPO_BN192_MULTI=0 disables, A/B runs)
+  static const bool bn192_multi = [] { const char* e = getenv("TOPO_BN192_MULTI"); return !(e && e[0] == '0'); }();
+  if (bn192_multi && n_seg > 1 && segs[0].r_pad == 0 && K < 1024 && (M + BM - 1) / BM >= sm_count()) {
+    bool all192 = true;
+    for (int i = 0; i < n_seg; ++i) all192 = all192 && segs[i].N % 192 == 0 && segs[i].act == TOPO_ACT_NONE;
+    if (all192) BN = 192;
+  }
   GemmParams p;
   memset(&p, 0, sizeof(p));
   uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -895,6 +907,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
     if (BN == 160) return launch_gemm<160, 32, 4, false>(p, grid, st);
     return launch_gemm<128, 32, 5, false>(p, grid, st);
   }
+  if (BN == 192) return launch_gemm<192, 0, 4, false>(p, grid, st);
   if (BN == 160) return launch_gemm<160, 0, 5, false>(p, grid, st);
   // BN = 256: a fourth stage (192 KB in flight) pays when the K loop is long (latency bound: 3 -> 4 stages took the
   // 3x3 convs from 930 to 1010-1380 TFLOP/s); short-K projections are epilogue bound and keep 3 stages
