@@ -6,14 +6,20 @@ ControlledUnetModel forward), the ldm ``DDIMSampler`` with batched classifier-fr
 ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs may import
 this module; the product package must never do so.
 
-PARITY UNPINNED: the arithmetic of this path lives in two git submodules that are empty in
+PARITY UNPINNED for the UNet / ControlNet / DDIM / VAE arithmetic: it lives in two git submodules that are empty in
 /root/reference (``ControlNet`` @ ed85cd1e25a5ed592f7d8178495b4483de0331bf and ``ctrlora`` @
-8940c941a00cc45da1154fc25ace5a7368a3b3a0, ``.SUBMODULES.json:8-21``) and the reference ships no
-tests, golden vectors or fixtures.  What *is* pinned: the LoRA linear algebra
-is checked against the reference's own importable ``LoRA_modified/LoRA_utils.py:20-42`` (fixtures in
-``tests/golden/lora_linear_*.pt`` generated by ``tests/golden/make_golden.py``); everything else
-restates the published upstream algorithm and is anchored on the reference's
-call sites, cited per function below.
+8940c941a00cc45da1154fc25ace5a7368a3b3a0, ``.SUBMODULES.json:8-21``) and the reference ships no tests, golden vectors
+or fixtures; those functions restate the published upstream algorithm and are
+anchored on the reference's call sites, cited per function below.  PINNED against the reference's own code, by fixtures
+generated from it in the build container (``tests/golden/make_golden.py``, checked by ``tests/test_oracle_golden.py``):
+
+* ``lora_linear``                — ``LoRA_modified/LoRA_utils.py:20-42`` outputs (``lora_linear.pt``)
+* ``lora_control_attention``     — the control branch, flatten order, scale and add-iff-shapes-match rule of
+  ``LoRA_modified/attention_lora.py:57-81`` (``control_lora.pt``; the upstream base class it subclasses is a stand-in)
+* ``control_lora_encoder``       — ``attention_lora.py:87-101`` outputs (``control_lora.pt``)
+* ``stitch_tiles`` / ``make_schedule`` — ``BaseModel/stitchTiles.py:13-41`` order (``stitch.pt``), schedule known answers
+* the drivers ``sample_preview`` / ``validate_step`` of the PRODUCT (``topo_b200.sampling``) are held to the reference's own
+  ``TextEncoder_Finetuning/vis_metrics.py:73-116,407-452`` run on a mock model (``drivers.pt``)
 
 The oracle is functional: it consumes a ``state_dict`` whose keys are the upstream key names (the
 product's module tree in ``topo_b200.ldm`` produces exactly those), so the same weights can be fed

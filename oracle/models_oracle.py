@@ -1,11 +1,16 @@
 """TEST INFRASTRUCTURE — fp32 PyTorch restatement of ``LoRA_modified/models.py`` (processor algebra + ControlLoRA
 pyramid), the checker for ``topo_b200/models.py``.  Never imported by the product package.
 
-PARITY UNPINNED for this file: the reference module imports ``diffusers`` (0.12-0.14 API, ``models.py:7-12``), which is
-not installed here, so it cannot be run to produce golden vectors and the reference ships no tests.  The functions
-below restate the reference line by line in functional form over the SAME parameter containers the CUDA path uses
-(anything with ``to_q/to_k/to_v/to_out`` Linears and ``to_*_lora.{down,up}`` pairs); citations are
-``LoRA_modified/models.py:<line>``.  Attention is the explicit ``softmax(q k^T * scale) v`` of
+PARITY PINNED on the reference's own processor code (round 2): ``tests/golden/make_golden_models.py`` runs
+``/root/reference/LoRA_modified/models.py`` itself — nine processor configurations and the ControlLoRA pyramid — and
+``tests/test_oracle_golden.py::test_models_oracle_matches_reference_models_py`` holds this file to those outputs at
+2e-5.  The reference module imports ``diffusers`` (0.12-0.14 API, ``models.py:7-12``), which is not installed here, so the
+few diffusers primitives it touches (``LoRALinearLayer``, the ``CrossAttention`` host module, ``Downsample2D``, the mixins)
+are STAND-INS restating diffusers 0.12 in the generator; everything the reference wrote on top of them (which tensor
+feeds which LoRA, skip flags, control-state entry points, pre/post stacks, concat / self-add / batch repeat, the pyramid
+wiring) is executed as is.  The functions below restate the reference line by line in functional form over the SAME
+parameter containers the CUDA path uses (anything with ``to_q/to_k/to_v/to_out`` Linears and ``to_*_lora.{down,up}``
+pairs); citations are ``LoRA_modified/models.py:<line>``.  Attention is the explicit ``softmax(q k^T * scale) v`` of
 ``get_attention_scores`` + ``torch.bmm`` (:143-144).
 """
 from __future__ import annotations
