@@ -96,6 +96,12 @@ int topo_attention(topo_handle_t h, const void* q, const void* k, const void* v,
  *     length are skipped.  This is the attention_mask of the BERT prompt encoder for right-padded prompts
  *     (tokenizer(padding="max_length"), LoRA_modified/multiseg_19prompts_batch1_shuffle_ctrlora.py:175-184);
  *     dp = 64 serves BERT-base's 12 x 64 heads.                                                              */
+/* topo_attention with the softmax row sum taken from the tensor core: the caller guarantees that V holds 1.0 in padded head
+ * column `l_col` of every head (d = 40 heads padded to 48: l_col = 40, produced for free by a bias entry of the V
+ * projection); the kernel then divides by O[:, l_col] instead of summing the probabilities in registers, and writes 0 to
+ * that output column.  Same result as topo_attention up to the bf16 rounding of P entering the sum.                    */
+int topo_attention_lcol(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq,
+                        int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, int l_col, void* stream);
 int topo_attention_varlen(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads,
                           int Nq, int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len,
                           void* stream);

@@ -20,7 +20,7 @@ ACT_NONE, ACT_SILU, ACT_GEGLU, ACT_GELU, ACT_RELU = 0, 1, 2, 3, 4
 # every symbol include/topo_b200.h declares (tests check the library exports all of them)
 SYMBOLS = [
     "topo_create", "topo_destroy", "topo_last_error", "topo_last_kernel", "topo_version", "topo_lora_linear", "topo_conv3x3",
-    "topo_attention", "topo_attention_varlen", "topo_embed_sum", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
+    "topo_attention", "topo_attention_lcol", "topo_attention_varlen", "topo_embed_sum", "topo_groupnorm_silu", "topo_groupnorm_ws_floats", "topo_layernorm",
     "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_ddim_step_x0", "topo_conv_direct",
     "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_tile_metrics", "topo_im2col3x3_s1_k64",
     "topo_add_bf16", "topo_tile_to_u8", "topo_tile_to_u8_round", "topo_softmax_rows", "topo_geglu_tile",
@@ -66,6 +66,7 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_lora_linear.argtypes = [vp, vp, i32, i32, i32, C.POINTER(TopoLinear), i32, vp]
     lib.topo_conv3x3.argtypes = [vp, vp, i32, i32, i32, i32, i32, C.POINTER(TopoLinear), vp]
     lib.topo_attention.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp]
+    lib.topo_attention_lcol.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, i32, vp]
     lib.topo_attention_varlen.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, f32, vp, vp]
     lib.topo_embed_sum.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     lib.topo_groupnorm_silu.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp, vp]

@@ -36,6 +36,8 @@ struct alignas(64) AttnParams {
   const int* kv_len;             // optional [B]: keys >= kv_len[b] are masked (right-padded prompts); nullptr = all Nk
   int Nq, Nk, heads, ldo;
   float scale_log2e;
+  int l_col;                     // >= 0: V carries a column of ones at this (padded) head column: the softmax row sum comes
+                                 // out of the P V UMMA as O[:, l_col] and is not accumulated by the softmax warps
 };
 
 // EARLY = true: the layout above (P in its own columns, S_{j+1} issued under softmax(j)).
@@ -207,6 +209,8 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     uint64_t* pv_done_b = &pv_done[st];
     const int nblk_st = st < nact ? nblk : 0;  // a stream without query rows idles
     float m_run = -INFINITY, l_run = 0.f;
+    constexpr int LCOL = 40;                                  // the ones column of a d = 40 head padded to 48
+    const bool lsum_mma = DP == 48 && p.l_col == LCOL;
     const float c = p.scale_log2e;
     constexpr float RESCALE_THRESHOLD = 8.0f;
 
@@ -258,23 +262,39 @@ attention_kernel(const __grid_constant__ AttnParams p) {
       }
       // ---- probabilities -> packed bf16 pairs (keys 2c, 2c+1 = TMEM column c of the P region)
       const float2 c2 = make_float2(c, c), nm2 = make_float2(-m_run, -m_run);
-      float2 ls[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
       uint32_t pk[ATT_BN / 2];
+      if (lsum_mma) {
+        // the row sum is the tensor core's job (ones column of V): one packed add per pair less on the issue-bound path
 #pragma unroll
-      for (int i = 0; i < ATT_BN; i += 2) {
-        const float2 x = ffma2(make_float2(sv[i], sv[i + 1]), c2, nm2);
-        float2 e;
-        if (((i >> 1) & 7) < NPOLY) {
-          e = exp2_poly2(x);
-        } else {
-          e.x = fast_exp2(x.x);
-          e.y = fast_exp2(x.y);
+        for (int i = 0; i < ATT_BN; i += 2) {
+          const float2 x = ffma2(make_float2(sv[i], sv[i + 1]), c2, nm2);
+          float2 e;
+          if (((i >> 1) & 7) < NPOLY) {
+            e = exp2_poly2(x);
+          } else {
+            e.x = fast_exp2(x.x);
+            e.y = fast_exp2(x.y);
+          }
+          pk[i >> 1] = pack_bf16x2(e.x, e.y);
         }
-        ls[(i >> 1) & 3] = fadd2(ls[(i >> 1) & 3], e);  // four independent packed sum chains
-        pk[i >> 1] = pack_bf16x2(e.x, e.y);
+      } else {
+        float2 ls[4] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+#pragma unroll
+        for (int i = 0; i < ATT_BN; i += 2) {
+          const float2 x = ffma2(make_float2(sv[i], sv[i + 1]), c2, nm2);
+          float2 e;
+          if (((i >> 1) & 7) < NPOLY) {
+            e = exp2_poly2(x);
+          } else {
+            e.x = fast_exp2(x.x);
+            e.y = fast_exp2(x.y);
+          }
+          ls[(i >> 1) & 3] = fadd2(ls[(i >> 1) & 3], e);  // four independent packed sum chains
+          pk[i >> 1] = pack_bf16x2(e.x, e.y);
+        }
+        const float2 lsum = fadd2(fadd2(ls[0], ls[1]), fadd2(ls[2], ls[3]));
+        l_run += lsum.x + lsum.y;
       }
-      const float2 lsum = fadd2(fadd2(ls[0], ls[1]), fadd2(ls[2], ls[3]));
-      l_run += lsum.x + lsum.y;
       if (j > 0) {
         mbar_wait(pv_done_b, (j - 1) & 1);  // P_{j-1} V_{j-1} finished (long ago): the P columns are free
         tc_fence_after();
@@ -289,13 +309,20 @@ attention_kernel(const __grid_constant__ AttnParams p) {
     mbar_wait(&pv_done[st], (nblk - 1) & 1);
     tc_fence_after();
     const int qrow = q0 + st * ATT_BM + row;
-    const float inv = 1.0f / l_run;
+    float inv = 1.0f / l_run;
+    if (DP == 48 && lsum_mma) {   // l = sum_j bf16(P_j) * 1.0, accumulated (and rescaled) in TMEM together with O
+      float t[16];
+      tmem_ld16(tmem_o + lane_addr + 32, t);
+      tmem_ld_wait();
+      inv = 1.0f / t[LCOL - 32];
+    }
     bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
 #pragma unroll
     for (int c0 = 0; c0 < DP; c0 += 16) {
       float t[16];
       tmem_ld16(tmem_o + lane_addr + c0, t);
       tmem_ld_wait();
+      if (DP == 48 && c0 == 32 && lsum_mma) t[LCOL - 32] = 0.f;   // the padded output columns stay zero
       if (qrow < p.Nq) {
         uint4 u0, u1;
         u0.x = pack_bf16x2(t[0] * inv, t[1] * inv);   u0.y = pack_bf16x2(t[2] * inv, t[3] * inv);
@@ -735,7 +762,9 @@ static int attn_npoly(int dp) {
 }
 
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
-                       int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len, cudaStream_t st) {
+                       int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len, int l_col, cudaStream_t st) {
+  TOPO_CHECK(l_col < 0 || (dp == 48 && l_col == 40 && Nk > XA_NKP), TOPO_E_INVAL,
+             "attention: the ones-column row sum is implemented for d = 40 heads padded to 48 (l_col = 40) on the flash kernel");
   TOPO_CHECK(dp == 48 || dp == 64 || dp == 80 || dp == 160, TOPO_E_INVAL,
              "attention: padded head dim must be 48, 64, 80 or 160 (got %d)", dp);
   TOPO_CHECK(((ldq | ldk | ldv | ldo) & 7) == 0, TOPO_E_INVAL, "attention: leading dims must be multiples of 8");
@@ -767,6 +796,7 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   p.heads = heads;
   p.ldo = ldo;
   p.scale_log2e = scale * 1.4426950408889634f;
+  p.l_col = l_col;
   // short key sequences (the 77-token prompt): the K/V-resident single-pass kernel.  TOPO_XATTN=0 keeps the flash kernel.
   static const bool xattn = [] { const char* e = getenv("TOPO_XATTN"); return !(e && e[0] == '0'); }();
   if (xattn && kv_len == nullptr && Nk <= XA_NKP && Nq >= ATT_BM && dp != 64) {

@@ -112,7 +112,7 @@ int make_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims
 int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* segs, int n_seg, cudaStream_t st);
 int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const topo_linear_t* seg, cudaStream_t st);
 int attention_dispatch(const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq, int Nk, int dp,
-                       int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len, cudaStream_t st);
+                       int ldq, int ldk, int ldv, int ldo, float scale, const int* kv_len, int l_col, cudaStream_t st);
 int embed_sum_dispatch(const int* ids, const float* word, const float* pos, const float* type0, void* y, int B, int T,
                        int C, int vocab, cudaStream_t st);
 int groupnorm_ws_floats(int B, int G);
@@ -229,7 +229,14 @@ int topo_attention(topo_handle_t h, const void* q, const void* k, const void* v,
                    int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, void* stream) {
   H_CHECK(h);
   TOPO_CHECK(q && k && v && o, TOPO_E_INVAL, "topo_attention: null argument");
-  return attention_dispatch(q, k, v, o, B, heads, Nq, Nk, dp, ldq, ldk, ldv, ldo, scale, nullptr, ST(stream));
+  return attention_dispatch(q, k, v, o, B, heads, Nq, Nk, dp, ldq, ldk, ldv, ldo, scale, nullptr, -1, ST(stream));
+}
+
+int topo_attention_lcol(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads, int Nq,
+                        int Nk, int dp, int ldq, int ldk, int ldv, int ldo, float scale, int l_col, void* stream) {
+  H_CHECK(h);
+  TOPO_CHECK(q && k && v && o, TOPO_E_INVAL, "topo_attention_lcol: null argument");
+  return attention_dispatch(q, k, v, o, B, heads, Nq, Nk, dp, ldq, ldk, ldv, ldo, scale, nullptr, l_col, ST(stream));
 }
 
 int topo_attention_varlen(topo_handle_t h, const void* q, const void* k, const void* v, void* o, int B, int heads,
@@ -237,7 +244,7 @@ int topo_attention_varlen(topo_handle_t h, const void* q, const void* k, const v
                           void* stream) {
   H_CHECK(h);
   TOPO_CHECK(q && k && v && o && kv_len, TOPO_E_INVAL, "topo_attention_varlen: null argument");
-  return attention_dispatch(q, k, v, o, B, heads, Nq, Nk, dp, ldq, ldk, ldv, ldo, scale, kv_len, ST(stream));
+  return attention_dispatch(q, k, v, o, B, heads, Nq, Nk, dp, ldq, ldk, ldv, ldo, scale, kv_len, -1, ST(stream));
 }
 
 int topo_embed_sum(topo_handle_t h, const int* ids, const float* word, const float* pos, const float* type0, void* y,

@@ -124,6 +124,11 @@ def pack_linear(mod: nn.Module, device, heads: int = 0, d: int = 0, dp: int = 0,
     return Lin(W.to(BF16).contiguous(), _dev(b, device, torch.float32), A, Bm, rp, s, r)
 
 
+def _lcol_enabled() -> bool:
+    import os
+    return os.environ.get("TOPO_ATTN_LCOL", "1") != "0"
+
+
 def pack_conv1x1(conv: nn.Conv2d, device) -> Lin:
     W = conv.weight.detach().to(device).reshape(conv.out_channels, conv.in_channels)
     return Lin(W.to(BF16).contiguous(), _dev(conv.bias, device, torch.float32))
@@ -255,6 +260,15 @@ class PAttn:
         self.v = pack_linear(attn.to_v, device, pad="rows", **kw)
         self.o = pack_linear(attn.to_out[0], device, pad="cols", **kw)
         self.module = attn  # for the optional to_control branch (CrossAttention_LoRA_Control)
+        # d = 40 self-attention (N up to 4096, the most expensive kernel of the step): the zero padding column 40 of every V
+        # head is set to 1.0 through the projection's bias, so the softmax row sum falls out of the P V UMMA (O[:, 40]) and
+        # the softmax warps do not accumulate it (ops.attention l_col).  TOPO_ATTN_LCOL=0 disables (A/B runs).
+        self.l_col = -1
+        if self.is_self and self.d == 40 and self.dp == 48 and _lcol_enabled():
+            bv = torch.zeros(self.hdp, dtype=torch.float32, device=device) if self.v.bias is None else self.v.bias.clone()
+            bv[torch.arange(self.heads, device=device) * self.dp + self.d] = 1.0
+            self.v.bias = bv
+            self.l_col = self.d
 
 
 class PBlock:
@@ -379,7 +393,8 @@ def run_attn(a: PAttn, n: torch.Tensor, h: torch.Tensor, B: int, kv) -> torch.Te
         k, v = kv
     Nk = k.shape[1]
     o = _rec("attn_self" if kv is None else "attn_cross", 4.0 * B * a.heads * N * Nk * a.d,
-             2.0 * (2 * M * hdp + 2 * B * Nk * hdp), lambda: ops.attention(q, k, v, a.heads, a.dp, a.scale),
+             2.0 * (2 * M * hdp + 2 * B * Nk * hdp),
+             lambda: ops.attention(q, k, v, a.heads, a.dp, a.scale, l_col=a.l_col if (kv is None and Nk > 80) else -1),
              f"B{B} N{N} Nk{Nk} d{a.d}")
     _count()
     out = gemm(o.view(M, hdp), a.o, res=h)

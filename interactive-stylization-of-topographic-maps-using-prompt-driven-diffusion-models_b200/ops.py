@@ -165,9 +165,10 @@ def conv3x3(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = Non
 
 
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp: int, scale: float,
-              kv_len: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+              kv_len: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, l_col: int = -1) -> torch.Tensor:
     """q [B,Nq,heads*dp], k/v [B,Nk,heads*dp] (bf16, padded head columns zero) -> o [B,Nq,heads*dp].
-    ``kv_len`` (int32 [B] on the device): keys at or beyond the sample's length are masked (right-padded prompts)."""
+    ``kv_len`` (int32 [B] on the device): keys at or beyond the sample's length are masked (right-padded prompts).
+    ``l_col >= 0``: v holds 1.0 in padded column ``l_col`` of every head and the row sum is read from the P V product."""
     _cuda(q, "attention")
     Bn, Nq, ld = q.shape
     Nk = k.shape[1]
@@ -180,6 +181,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, dp:
             capi.handle(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), Bn, heads, Nq, Nk, dp,
             q.stride(1), k.stride(1), v.stride(1), o.stride(1), scale, kv_len.data_ptr(), capi.stream()),
             "topo_attention_varlen")
+        return o
+    if l_col >= 0:
+        capi.check(capi.load_library().topo_attention_lcol(
+            capi.handle(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), Bn, heads, Nq, Nk, dp,
+            q.stride(1), k.stride(1), v.stride(1), o.stride(1), scale, l_col, capi.stream()), "topo_attention_lcol")
         return o
     capi.check(capi.load_library().topo_attention(
         capi.handle(), q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), Bn, heads, Nq, Nk, dp,

@@ -107,3 +107,36 @@ def test_cross_attention_strided_views_and_out():
         ops.attention(q, k[sl], v[sl], heads, dp, d ** -0.5, out=out[sl])
         ref = _ref(q, k[sl].contiguous(), v[sl].contiguous(), heads, d, dp, d ** -0.5)
         assert_close(out[sl].float().reshape(B // 2, N, heads, dp)[..., :d], ref, TOL, f"cross-attention slice {i}")
+
+
+@pytest.mark.parametrize("B,N", [(2, 4096), (3, 320), (1, 128)])
+def test_attention_row_sum_from_ones_column(B, N):
+    """topo_attention_lcol: V carries 1.0 in padded column 40 of every d = 40 head, the kernel takes the softmax row sum
+    from the P V product (O[:, 40]) instead of accumulating it in the softmax warps; same result as the explicit sum, and
+    the padded output columns (incl. column 40) stay zero."""
+    from topo_b200 import ops
+    heads, d, dp = 8, 40, 48
+    q, k, v = _mk(B, N, heads, d, dp, 31), _mk(B, N, heads, d, dp, 32), _mk(B, N, heads, d, dp, 33)
+    v1 = v.clone().reshape(B, N, heads, dp)
+    v1[..., d] = 1.0
+    v1 = v1.reshape(B, N, heads * dp)
+    scale = d ** -0.5
+    o = ops.attention(q, k, v1, heads, dp, scale, l_col=d)
+    plain = ops.attention(q, k, v, heads, dp, scale)
+    ref = _ref(q, k, v, heads, d, dp, scale)
+    got = o.float().reshape(B, N, heads, dp)
+    assert_close(got[..., :d], ref, TOL, f"attention l_col B{B} N{N}")
+    assert got[..., d:].abs().max() == 0, "padded head columns (incl. the ones column) must stay zero"
+    assert_close(o, plain, 1e-2, "ones-column sum vs explicit sum")
+
+
+def test_attention_row_sum_from_ones_column_peaked():
+    from topo_b200 import ops
+    B, heads, N, d, dp = 1, 2, 512, 40, 48
+    q, k, v = _mk(B, N, heads, d, dp, 1), _mk(B, N, heads, d, dp, 2), _mk(B, N, heads, d, dp, 3)
+    q = (q.float() * 60.0).to(BF16)
+    v1 = v.clone().reshape(B, N, heads, dp)
+    v1[..., d] = 1.0
+    o = ops.attention(q, k, v1.reshape(B, N, heads * dp), heads, dp, d ** -0.5, l_col=d)
+    ref = _ref(q, k, v, heads, d, dp, d ** -0.5)
+    assert_close(o.float().reshape(B, N, heads, dp)[..., :d], ref, 3e-2, "attention l_col peaked (rescale path)")
