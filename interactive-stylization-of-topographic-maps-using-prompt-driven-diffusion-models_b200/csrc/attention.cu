@@ -40,6 +40,19 @@ struct alignas(64) AttnParams {
                                  // out of the P V UMMA as O[:, l_col] and is not accumulated by the softmax warps
 };
 
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
 // EARLY = true: the layout above (P in its own columns, S_{j+1} issued under softmax(j)).
 // EARLY = false: P_j is written over S_j (columns [0,32)) and the issuer runs P_j V_j, then S_{j+1}: a stream then needs
 // only 64 + dp columns, so FOUR one-stream CTAs share an SM at dp = 48 — the better shape for the 77-key cross-attention
@@ -346,6 +359,291 @@ attention_kernel(const __grid_constant__ AttnParams p) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// K2s — the N = 4096, d = 40 self-attention with TWO threads per query row.
+//
+// ncu on attention_kernel<48,3,2,1> (profiles/r02e_ncu_attention_B8.txt): 4 resident warps per scheduler, an eligible warp on
+// 54 % of the cycles only, stalls led by fixed-latency dependencies ("wait"), the MUFU queue and scoreboards — neither the
+// XU pipe (48 %) nor the issue slots (54 %) are saturated: the kernel is short of warps, and at 117 registers (64 S values
+// per thread) it cannot have more.  Here every 64-key block of a 128-row stream is shared by EIGHT softmax warps: the two
+// warps that can reach a TMEM lane quadrant each take 32 of the 64 columns, i.e. 32 S values and 16 packed P words per
+// thread, which fits 8 x NS + NS + 1 warps in the register file.  The two halves of a row need the same running maximum:
+// each thread publishes the maximum of its half in shared memory and the pair meets at a 64-thread named barrier (one
+// hardware barrier per (stream, quadrant)); the row SUM needs no exchange at all — it comes out of the P V UMMA through
+// the ones column of V (topo_attention_lcol).  Producer and issuer warps, the K/V ring, the TMEM layout
+// (S 64 | P 32 | O 48 columns per stream) and the lazy O rescale are those of attention_kernel.
+template <int NS>
+struct AttnSplitSmem {
+  static constexpr int DP = 48;
+  static constexpr int THREADS = 32 * (1 + NS + 8 * NS);
+  static constexpr int Q_BYTES = ATT_BM * 128, KV_BYTES = ATT_BN * 128;
+  static constexpr int RING = 4;
+  static constexpr int BAR_OFF = NS * Q_BYTES + RING * KV_BYTES;
+  static constexpr int XCH_OFF = BAR_OFF + 256;            // float [NS][2 parities][2 halves][128 rows]
+  static constexpr int TOTAL = XCH_OFF + NS * 2 * 2 * ATT_BM * 4;
+  static constexpr uint32_t P_COL = ATT_BN, O_COL = ATT_BN + ATT_BN / 2, STREAM_COLS = O_COL + DP;
+  static constexpr uint32_t TMEM_COLS = NS * STREAM_COLS <= 256 ? 256 : 512;
+  static_assert(NS * STREAM_COLS <= 512, "TMEM");
+  static_assert(1 + 4 * NS <= 16, "one named barrier per (stream, quadrant)");
+};
+
+template <int NS, int NPOLY>
+__global__ void __launch_bounds__(AttnSplitSmem<NS>::THREADS, 1) attention_split_kernel(const __grid_constant__ AttnParams p) {
+  using L = AttnSplitSmem<NS>;
+  constexpr int DP = L::DP, RING = L::RING, LCOL = 40;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* q_tiles = smem;
+  uint8_t* ring = smem + NS * L::Q_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* q_full = bars;
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = kv_full + RING;
+  uint64_t* s_full = kv_empty + RING;
+  uint64_t* s_free = s_full + NS;        // 256 arrivals
+  uint64_t* p_ready = s_free + NS;       // 256 arrivals
+  uint64_t* pv_done = p_ready + NS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pv_done + NS);
+  float* xch = reinterpret_cast<float*>(smem + L::XCH_OFF);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * (ATT_BM * NS);
+  const int head = blockIdx.y;
+  const int b = blockIdx.z;
+  const int Nk = p.Nk;
+  const int nblk = (Nk + ATT_BN - 1) / ATT_BN;
+  const int col0 = head * DP;
+  const int nact = min(NS, (p.Nq - q0 + ATT_BM - 1) / ATT_BM);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tm_q);
+    tma_prefetch_desc(&p.tm_k);
+    tma_prefetch_desc(&p.tm_v);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < RING; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_empty[i], nact);
+    }
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 256);
+      mbar_init(&p_ready[i], 256);
+      mbar_init(&pv_done[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, L::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer (as attention_kernel) =====================
+    if (lane == 0) {
+      mbar_expect_tx(q_full, nact * L::Q_BYTES);
+      for (int st = 0; st < nact; ++st) tma_load_3d(q_tiles + st * L::Q_BYTES, &p.tm_q, q_full, col0, q0 + st * ATT_BM, b);
+      const int ntiles = 2 * nblk;  // K0 V0 K1 V1 ...
+      for (int i = 0; i < ntiles; ++i) {
+        const int slot = i % RING;
+        const uint32_t ph = (i / RING) & 1;
+        mbar_wait(&kv_empty[slot], ph ^ 1);
+        mbar_expect_tx(&kv_full[slot], L::KV_BYTES);
+        tma_load_3d(ring + slot * L::KV_BYTES, (i & 1) ? &p.tm_v : &p.tm_k, &kv_full[slot], col0, (i >> 1) * ATT_BN, b);
+      }
+    }
+  } else if (warp <= NS) {
+    // ===================== MMA issuer of stream warp-1 (as attention_kernel, EARLY) =====================
+    const int st = warp - 1;
+    if (lane == 0 && st < nact) {
+      const uint32_t tmem_s = tmem_base + st * L::STREAM_COLS;
+      const uint32_t tmem_p = tmem_s + L::P_COL;
+      const uint32_t tmem_o = tmem_s + L::O_COL;
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, ATT_BN, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DP, 0, 1);
+      const uint32_t q_s = smem_u32(q_tiles + st * L::Q_BYTES);
+      auto issue_s = [&](int j) {
+        const int t = 2 * j, slot = t % RING;
+        mbar_wait(&kv_full[slot], (t / RING) & 1);
+        tc_fence_after();
+        const uint32_t k_s = smem_u32(ring + slot * L::KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < DP / 16; ++k)
+          umma_bf16(tmem_s, kmajor_desc(q_s + k * 32, 128), kmajor_desc(k_s + k * 32, 128), idesc_s, k != 0);
+        umma_commit(&s_full[st]);
+        umma_commit(&kv_empty[slot]);
+      };
+      mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < nblk; ++j) {
+        if (j + 1 < nblk) {
+          mbar_wait(&s_free[st], j & 1);
+          tc_fence_after();
+          issue_s(j + 1);
+        }
+        mbar_wait(&p_ready[st], j & 1);
+        const int t = 2 * j + 1, slot = t % RING;
+        mbar_wait(&kv_full[slot], (t / RING) & 1);
+        tc_fence_after();
+        const uint32_t v_s = smem_u32(ring + slot * L::KV_BYTES);
+#pragma unroll
+        for (int k = 0; k < ATT_BN / 16; ++k)
+          umma_bf16_ts(tmem_o, tmem_p + k * 8, mnmajor_sw128_desc(v_s + k * 2048, L::KV_BYTES), idesc_pv, (j | k) != 0);
+        umma_commit(&pv_done[st]);
+        umma_commit(&kv_empty[slot]);
+      }
+    }
+  } else {
+    // ===================== softmax: 8 warps per stream, 2 threads per query row =====================
+    const int sw = warp - 1 - NS;
+    const int st = sw >> 3;
+    const int half = (sw >> 2) & 1;     // which 32 of the block's 64 key columns
+    const int qd = warp & 3;            // the TMEM lane quadrant a warp can reach is warp % 4
+    const int row = qd * 32 + lane;
+    const uint32_t lane_addr = static_cast<uint32_t>(qd * 32) << 16;
+    const uint32_t tmem_s = tmem_base + st * L::STREAM_COLS + lane_addr;
+    const uint32_t tmem_p = tmem_s + L::P_COL;
+    const uint32_t tmem_o = tmem_s + L::O_COL;
+    // pair barrier: the two warps of (stream, quadrant).  warp & 3 enumerates the quadrants of a stream's 8 consecutive warps
+    const int pair_bar = 1 + st * 4 + qd;
+    float* xs = xch + st * (2 * 2 * ATT_BM);
+    const int nblk_st = st < nact ? nblk : 0;
+    float m_run = -INFINITY;
+    const float c = p.scale_log2e;
+    constexpr float RESCALE_THRESHOLD = 8.0f;
+
+    for (int j = 0; j < nblk_st; ++j) {
+      const int kvalid = min(ATT_BN, Nk - j * ATT_BN) - half * 32;   // valid columns of this thread's half
+      mbar_wait(&s_full[st], j & 1);
+      tc_fence_after();
+      float sv[32];
+      tmem_ld32(tmem_s + half * 32, sv);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_free[st]);
+      if (kvalid < 32) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i >= kvalid) sv[i] = -INFINITY;
+      }
+      float m0 = fmax3(sv[0], sv[1], sv[2]), m1 = fmax3(sv[3], sv[4], sv[5]), m2 = fmax3(sv[6], sv[7], sv[8]), m3 = fmax3(sv[9], sv[10], sv[11]);
+#pragma unroll
+      for (int i = 12; i < 28; i += 8) {
+        m0 = fmax3(m0, sv[i], sv[i + 1]);
+        m1 = fmax3(m1, sv[i + 2], sv[i + 3]);
+        m2 = fmax3(m2, sv[i + 4], sv[i + 5]);
+        m3 = fmax3(m3, sv[i + 6], sv[i + 7]);
+      }
+      m0 = fmax3(m0, sv[28], sv[29]);
+      m1 = fmax3(m1, sv[30], sv[31]);
+      const float mx_half = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+      // ---- the row maximum of the block = max of the two halves: publish, meet the partner warp, read
+      float* slot = xs + (j & 1) * (2 * ATT_BM);
+      slot[half * ATT_BM + row] = mx_half;
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      const float mx = fmaxf(mx_half, slot[(half ^ 1) * ATT_BM + row]);
+      const float m_new = fmaxf(m_run, mx * c);
+      const bool need = j > 0 && m_new > m_run + RESCALE_THRESHOLD;
+      if (j == 0) m_run = m_new;
+      if (j > 0 && __any_sync(0xffffffffu, need)) {
+        // both warps of the pair see the same rows and the same maxima, so they take this branch together; each
+        // rescales its share of the O columns ([0,32) / [32,48))
+        mbar_wait(&pv_done[st], (j - 1) & 1);
+        tc_fence_after();
+        const float alpha = need ? fast_exp2(m_run - m_new) : 1.0f;
+        if (need) m_run = m_new;
+        const int c_lo = half ? 32 : 0, c_hi = half ? DP : 32;
+        for (int c0 = c_lo; c0 < c_hi; c0 += 16) {
+          float t[16];
+          tmem_ld16(tmem_o + c0, t);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) t[i] *= alpha;
+          tmem_st16(tmem_o + c0, t);
+        }
+      }
+      // ---- probabilities -> packed bf16 pairs; the row sum is the tensor core's job (ones column of V)
+      const float2 c2 = make_float2(c, c), nm2 = make_float2(-m_run, -m_run);
+      uint32_t pk[16];
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        const float2 x = ffma2(make_float2(sv[i], sv[i + 1]), c2, nm2);
+        float2 e;
+        if (((i >> 1) & 7) < NPOLY) {
+          e = exp2_poly2(x);
+        } else {
+          e.x = fast_exp2(x.x);
+          e.y = fast_exp2(x.y);
+        }
+        pk[i >> 1] = pack_bf16x2(e.x, e.y);
+      }
+      if (j > 0) {
+        mbar_wait(&pv_done[st], (j - 1) & 1);  // P_{j-1} V_{j-1} finished (long ago): the P columns are free
+        tc_fence_after();
+      }
+      tmem_st16u(tmem_p + half * 16, pk);
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&p_ready[st]);
+    }
+    // ---- last block's P V, normalise by O[:, 40] (= sum of the bf16 probabilities), store this thread's columns
+    if (st < nact) {
+      mbar_wait(&pv_done[st], (nblk - 1) & 1);
+      tc_fence_after();
+      const int qrow = q0 + st * ATT_BM + row;
+      float hi[16];
+      tmem_ld16(tmem_o + 32, hi);
+      tmem_ld_wait();
+      const float inv = 1.0f / hi[LCOL - 32];
+      bf16* dst = p.o + ((size_t)b * p.Nq + qrow) * p.ldo + col0;
+      if (half == 0) {
+        float t[32];
+        tmem_ld32(tmem_o, t);
+        tmem_ld_wait();
+        if (qrow < p.Nq) {
+#pragma unroll
+          for (int c0 = 0; c0 < 32; c0 += 8) {
+            uint4 u;
+            u.x = pack_bf16x2(t[c0 + 0] * inv, t[c0 + 1] * inv); u.y = pack_bf16x2(t[c0 + 2] * inv, t[c0 + 3] * inv);
+            u.z = pack_bf16x2(t[c0 + 4] * inv, t[c0 + 5] * inv); u.w = pack_bf16x2(t[c0 + 6] * inv, t[c0 + 7] * inv);
+            *reinterpret_cast<uint4*>(dst + c0) = u;
+          }
+        }
+      } else if (qrow < p.Nq) {
+        hi[LCOL - 32] = 0.f;   // the padded output columns stay zero
+        uint4 u0, u1;
+        u0.x = pack_bf16x2(hi[0] * inv, hi[1] * inv);   u0.y = pack_bf16x2(hi[2] * inv, hi[3] * inv);
+        u0.z = pack_bf16x2(hi[4] * inv, hi[5] * inv);   u0.w = pack_bf16x2(hi[6] * inv, hi[7] * inv);
+        u1.x = pack_bf16x2(hi[8] * inv, hi[9] * inv);   u1.y = pack_bf16x2(hi[10] * inv, hi[11] * inv);
+        u1.z = pack_bf16x2(hi[12] * inv, hi[13] * inv); u1.w = pack_bf16x2(hi[14] * inv, hi[15] * inv);
+        *reinterpret_cast<uint4*>(dst + 32) = u0;
+        *reinterpret_cast<uint4*>(dst + 40) = u1;
+      }
+    }
+    __syncwarp();
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, L::TMEM_COLS);
+  }
+}
+
+template <int NS, int NPOLY>
+static int launch_attention_split(const AttnParams& p, int B, cudaStream_t st) {
+  using L = AttnSplitSmem<NS>;
+  auto kfn = attention_split_kernel<NS, NPOLY>;
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
+  dim3 grid((p.Nq + ATT_BM * NS - 1) / (ATT_BM * NS), p.heads, B);
+  kfn<<<grid, L::THREADS, L::TOTAL, st>>>(p);
+  TOPO_CUDA(cudaGetLastError());
+  note_kernel("attention_split_kernel<%d, %d>", NS, NPOLY);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // K3 — cross-attention over a SHORT key sequence (the 77-token prompt; Nk <= 80), HBM bound: q in, o out, nothing else.
 //
 // The flash kernel above treats the prompt as two 64-key blocks and pays, per 128-query tile, a CTA launch, a TMEM
@@ -386,19 +684,6 @@ struct XAttnSmem {
   static_assert(CTAS * (TOTAL + 1024) <= 228 * 1024, "smem");
 };
 
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* r) {
-  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r[0]),
-               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
-               : "memory");
-}
-__device__ __forceinline__ void tmem_st16u(uint32_t taddr, const uint32_t* r) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
-      : "memory");
-}
 // TMA store of a dense shared-memory box (no swizzle) to a 3-D tensor; rows / columns outside the tensor are clipped
 __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
   asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
@@ -827,6 +1112,18 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   const int np = attn_npoly(dp);
   const int ns = attn_streams(dp, Nq);
   if (dp == 48) {
+    // two threads per query row (8 softmax warps per stream) for the long self-attentions that carry the ones column;
+    // TOPO_ATTN_SPLIT = <streams><poly eighths> (e.g. 32, 33, 22; 0 = off) for A/B runs
+    static const int split = [] { const char* e = getenv("TOPO_ATTN_SPLIT"); return e ? atoi(e) : 32; }();
+    if (split > 0 && l_col == 40 && kv_len == nullptr && Nk >= 4 * ATT_BN && Nq >= 3 * ATT_BM) {
+      switch (split) {
+        case 22: return launch_attention_split<2, 2>(p, B, st);
+        case 23: return launch_attention_split<2, 3>(p, B, st);
+        case 33: return launch_attention_split<3, 3>(p, B, st);
+        case 34: return launch_attention_split<3, 4>(p, B, st);
+        default: return launch_attention_split<3, 2>(p, B, st);
+      }
+    }
     if (Nk <= 2 * ATT_BN && !getenv("TOPO_ATTN_NOALIAS")) return launch_attention<48, 1, 0, false>(p, B, st);
     if (ns == 1) return np ? launch_attention<48, 1, 2>(p, B, st) : launch_attention<48, 1, 0>(p, B, st);
     if (ns == 2) return np ? launch_attention<48, 2, 2>(p, B, st) : launch_attention<48, 2, 0>(p, B, st);

@@ -109,11 +109,12 @@ def test_cross_attention_strided_views_and_out():
         assert_close(out[sl].float().reshape(B // 2, N, heads, dp)[..., :d], ref, TOL, f"cross-attention slice {i}")
 
 
-@pytest.mark.parametrize("B,N", [(2, 4096), (3, 320), (1, 128)])
+@pytest.mark.parametrize("B,N", [(2, 4096), (3, 320), (1, 128), (2, 1024), (3, 640), (1, 448)])
 def test_attention_row_sum_from_ones_column(B, N):
     """topo_attention_lcol: V carries 1.0 in padded column 40 of every d = 40 head, the kernel takes the softmax row sum
     from the P V product (O[:, 40]) instead of accumulating it in the softmax warps; same result as the explicit sum, and
-    the padded output columns (incl. column 40) stay zero."""
+    the padded output columns (incl. column 40) stay zero.  N >= 384 selects attention_split_kernel (two threads per query
+    row); N = 640 / 448 leave the last CTA with inactive streams and a ragged last key block."""
     from topo_b200 import ops
     heads, d, dp = 8, 40, 48
     q, k, v = _mk(B, N, heads, d, dp, 31), _mk(B, N, heads, d, dp, 32), _mk(B, N, heads, d, dp, 33)
