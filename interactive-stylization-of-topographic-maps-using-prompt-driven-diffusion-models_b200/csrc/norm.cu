@@ -438,8 +438,11 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
   // HBM twice (100 MB at the 64x64 level: ncu shows 32-34 % DRAM throughput on BOTH passes); run as statistics + apply per
   // CHUNK of samples that fits the L2, the second read of a chunk is an L2 hit and the pair moves 4 instead of 6 bytes
   // per element through HBM.  Per-sample results do not depend on the chunking (statistics slabs are a function of
-  // (HW, C) only; apply is element-wise).  TOPO_GN_CHUNK_MB=0 restores the two whole-batch launches (A/B runs).
-  static const long long chunk_bytes = [] { const char* e = getenv("TOPO_GN_CHUNK_MB"); return (long long)(e ? atoi(e) : 40) << 20; }();
+  // (HW, C) only; apply is element-wise).  MEASURED AND NOT ENABLED (profiles/r02g_gn_bench.txt): with 24 / 40 / 64 MB chunks
+  // the six large shapes of a step take 1150 / 887 / 781 us against 611 us for the two whole-batch launches — the L2 does
+  // not keep a chunk resident against the y write stream, and the extra launches add tails.  TOPO_GN_CHUNK_MB=<MB> turns
+  // it on for A/B runs; the default (0) is the whole-batch pair.
+  static const long long chunk_bytes = [] { const char* e = getenv("TOPO_GN_CHUNK_MB"); return (long long)(e ? atoi(e) : 0) << 20; }();
   const long long sample_bytes = (long long)HW * C * 2;
   int Bc = B;
   if (chunk_bytes > 0 && sample_bytes * B > chunk_bytes + chunk_bytes / 2) {
