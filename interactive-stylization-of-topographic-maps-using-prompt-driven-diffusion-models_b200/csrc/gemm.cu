@@ -875,7 +875,8 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   // CTA pairs (cta_group::2, six 32 KB stages) for the long-K, pipeline-latency-bound problems with at least one pair
   // tile per cluster; short-K projections are epilogue bound and lose from coupling two epilogues to one issuer
   // (measured: K = 1280 / 2560 -> +5 / +9 %, K = 320 GEGLU -> -16 %)
-  const bool pair = BN == 256 && r_pad == 0 && K >= 1024 && pair_enabled() &&
+  static const int pair_min_k = [] { const char* e = getenv("TOPO_PAIR_MINK"); return e ? atoi(e) : 1024; }();   // A/B runs
+  const bool pair = BN == 256 && r_pad == 0 && K >= pair_min_k && pair_enabled() &&
                     ((M + 2 * BM - 1) / (2 * BM)) >= sm_count() / 2;
   // the 320-wide single-accumulator tile pays on the 45+-block K loops of the convs (273 -> 247 us) but not here: with
   // K = 1280 the un-overlapped epilogue costs more than the second A load (152 -> 160 us); TOPO_BN320=2 forces it
