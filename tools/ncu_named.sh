@@ -9,15 +9,15 @@ tag=${1:-r02}
 variant=${2:-ctrlora}
 mkdir -p gpurun_out
 python tools/profile_step.py 38 $variant > gpurun_out/${tag}_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${tag}_plain.log; exit 1; }
-run() {  # name regex skip count
-  ncu --set full --clock-control none --import-source on --profile-from-start off -k "regex:$2" -s $3 -c $4 \
+run() {  # name regex(on the demangled name) skip count
+  ncu --set full --clock-control none --import-source on --profile-from-start off --kernel-name-base demangled -k "regex:$2" -s $3 -c $4 \
       -f -o gpurun_out/${tag}_$1 python tools/profile_step.py 38 $variant > gpurun_out/${tag}_$1.log 2>&1
-  echo "$1 rc=$?"
+  echo "$1 rc=$? $(grep -c '==PROF== Profiling' gpurun_out/${tag}_$1.log) launches profiled"
 }
-run lora    'gemm_kernel<[0-9]+, (16|32),' 0 6
-run attn    'attention_kernel<(48|80|160), [23]' 1 6
-run xattn   'cross_attention_kernel|attention_kernel<(48|80|160), 1' 0 6
+run lora    'gemm_kernel<\(int\)[0-9]+, \(int\)(16|32),' 0 6
+run attn    'attention_split_kernel|attention_kernel<\(int\)(80|160), \(int\)2' 1 6
+run xattn   'cross_attention_kernel' 0 6
 run gn      'gn_(stats|apply|small)_kernel' 0 8
 run ln      'layernorm' 0 4
-run conv    'gemm_kernel<(256|320), 0, [0-9], 1, 1>' 2 4
-run proj    'gemm_kernel<(160|256|128), 0, [0-9], 0, [01]>' 8 8
+run conv    'gemm_kernel<\(int\)(256|320), \(int\)0, \(int\)[0-9], \(bool\)1, \(bool\)1>' 2 4
+run proj    'gemm_kernel<\(int\)(128|160|192|256), \(int\)0, \(int\)[0-9], \(bool\)0, \(bool\)[01]>' 8 10
