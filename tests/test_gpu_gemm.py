@@ -106,3 +106,53 @@ def test_conv3x3_implicit_gemm(B, H, W, Cin, Cout):
     y = ops.conv3x3(x, w, b, rowbias=emb)
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), b, padding=1) + emb[:, :, None, None]
     assert_close(y.float().permute(0, 3, 1, 2), ref, TOL, f"conv3x3 {B}x{H}x{W} {Cin}->{Cout}")
+
+
+@pytest.mark.parametrize("M,K,N,r,nseg,res", [
+    (148 * 128 + 70, 320, 320, 16, 1, True),     # 160-wide LoRA tiles, contiguous chunks that cross (row tile) groups, ragged M
+    (148 * 128 * 2, 320, 384, 8, 3, False),      # fused q/k/v, 192-wide LoRA tiles: groups change with the SEGMENT inside a row tile
+    (9728, 1280, 1280, 32, 1, True),             # r_pad 32, K = 20 blocks (pre-pass longer than the ring), 8 n tiles per group
+    (38912, 640, 640, 4, 3, False),              # 160-wide, three segments
+    (640, 384, 200, 12, 1, True),                # 128-wide fallback (N not a multiple of 160/192), ragged N tile, strided walk
+    (128, 64, 16, 16, 1, False),                 # one tile, one K block
+])
+def test_lora_prepass_walks(M, K, N, r, nseg, res):
+    """K1 round 2: T = x A^T comes from a pre-pass issued one tile ahead of each (row tile, segment) group and every tile
+    starts from (sT) B^T.  Shapes chosen so that a CTA's tile chunk begins / ends in the middle of a group, groups change by
+    segment and by row tile, the pre-pass is longer than the stage ring, and the strided (one tile per CTA) walk is hit."""
+    from topo_b200 import capi
+    ops = _ops()
+    x = rnd(M, K, seed=1).to(BF16)
+    out = torch.zeros(M, nseg * N, dtype=BF16, device="cuda")
+    rs = rnd(M, N, seed=2).to(BF16) if res else None
+    segs, refs, keep = [], [], []
+    xf = x.float()
+    for i in range(nseg):
+        W = rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16)
+        A, Bm = rnd(r, K, seed=20 + i, scale=K ** -0.5), rnd(N, r, seed=30 + i, scale=0.3)
+        Ap, Bp, rp = ops.prep_lora(A, Bm)
+        b = rnd(N, seed=40 + i)
+        keep += [W, Ap, Bp, b]
+        segs.append(capi.make_linear(W, out, N, bias=b, A=Ap, B=Bp, r_pad=rp, s=1.5, out_ld=nseg * N, out_col=i * N,
+                                     res=rs if nseg == 1 else None, res_ld=0 if rs is None else rs.stride(0)))
+        ref = xf @ W.float().t() + b + 1.5 * ((xf @ bf(A).t()) @ bf(Bm).t())
+        delta = 1.5 * ((xf @ bf(A).t()) @ bf(Bm).t())
+        assert delta.abs().max() > 0.05 * ref.abs().max()
+        refs.append(ref + (rs.float() if (res and nseg == 1) else 0))
+    ops.lora_linear_raw(x, M, K, K, segs)
+    print(f"[parity] LoRA pre-pass M{M} K{K} N{nseg}x{N} r{r}: {capi.last_kernel()}")
+    assert_close(out, torch.cat(refs, 1), TOL, f"LoRA pre-pass M{M} K{K} N{nseg}x{N} r{r}")
+
+
+def test_fused_qkv_plain_192_wide_tiles():
+    """Three bias-free segments of 384 columns at large M: the 192-wide tile path of the level-0 q/k/v projection."""
+    from topo_b200 import capi
+    ops = _ops()
+    M, K, N = 148 * 128 + 5, 320, 384
+    x = rnd(M, K, seed=1).to(BF16)
+    out = torch.zeros(M, 3 * N, dtype=BF16, device="cuda")
+    Ws = [rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16) for i in range(3)]
+    segs = [capi.make_linear(W, out, N, out_ld=3 * N, out_col=i * N) for i, W in enumerate(Ws)]
+    ops.lora_linear_raw(x, M, K, K, segs)
+    assert capi.last_kernel() == "gemm_kernel<192, 0, 4, 0, 0>", capi.last_kernel()
+    assert_close(out, torch.cat([x.float() @ W.float().t() for W in Ws], 1), TOL, "fused qkv, 192-wide tiles")
