@@ -1117,6 +1117,8 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
     static const int split = [] { const char* e = getenv("TOPO_ATTN_SPLIT"); return e ? atoi(e) : 33; }();
     if (split > 0 && l_col == 40 && kv_len == nullptr && Nk >= 4 * ATT_BN && Nq >= 3 * ATT_BM) {
       switch (split) {
+        case 30: return launch_attention_split<3, 0>(p, B, st);
+        case 31: return launch_attention_split<3, 1>(p, B, st);
         case 22: return launch_attention_split<2, 2>(p, B, st);
         case 23: return launch_attention_split<2, 3>(p, B, st);
         case 34: return launch_attention_split<3, 4>(p, B, st);
