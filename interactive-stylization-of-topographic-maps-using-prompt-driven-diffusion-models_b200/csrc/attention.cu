@@ -1113,17 +1113,18 @@ int attention_dispatch(const void* q, const void* k, const void* v, void* o, int
   const int ns = attn_streams(dp, Nq);
   if (dp == 48) {
     // two threads per query row (8 softmax warps per stream) for the long self-attentions that carry the ones column;
-    // TOPO_ATTN_SPLIT = <streams><poly eighths> (e.g. 32, 33, 22; 0 = off) for A/B runs
-    static const int split = [] { const char* e = getenv("TOPO_ATTN_SPLIT"); return e ? atoi(e) : 33; }();
+    // TOPO_ATTN_SPLIT = <streams><poly eighths> (30..34, 22, 23; 0 = off) for A/B runs.  Measured at B38 h8 N4096
+    // (profiles/r02i_attn_bench.txt): 3 streams with 0/1/2/3/4 of 8 pairs on the polynomial = 1627/1577/1633/1620/1713 us
+    static const int split = [] { const char* e = getenv("TOPO_ATTN_SPLIT"); return e ? atoi(e) : 31; }();
     if (split > 0 && l_col == 40 && kv_len == nullptr && Nk >= 4 * ATT_BN && Nq >= 3 * ATT_BM) {
       switch (split) {
         case 30: return launch_attention_split<3, 0>(p, B, st);
-        case 31: return launch_attention_split<3, 1>(p, B, st);
+        case 33: return launch_attention_split<3, 3>(p, B, st);
         case 22: return launch_attention_split<2, 2>(p, B, st);
         case 23: return launch_attention_split<2, 3>(p, B, st);
         case 34: return launch_attention_split<3, 4>(p, B, st);
         case 32: return launch_attention_split<3, 2>(p, B, st);
-        default: return launch_attention_split<3, 3>(p, B, st);
+        default: return launch_attention_split<3, 1>(p, B, st);
       }
     }
     if (Nk <= 2 * ATT_BN && !getenv("TOPO_ATTN_NOALIAS")) return launch_attention<48, 1, 0, false>(p, B, st);
