@@ -1,6 +1,8 @@
 #!/bin/bash
-# GPU call 11 (round 2): FINAL build (split attention default <3,1>): full -m gpu suite, smoke, default bench line, ncu of the attention family
+# GPU call 11 (round 2): FINAL build (split attention default <3,1>): test_zz_no_alloc alone in a fresh process, then the full -m gpu suite (it runs last there), smoke, default bench line, ncu of the attention family
 mkdir -p gpurun_out
+(timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -p no:cacheprovider > gpurun_out/r02y_no_alloc_alone.txt 2>&1; echo "pytest rc=$?" >> gpurun_out/r02y_no_alloc_alone.txt)
+tail -4 gpurun_out/r02y_no_alloc_alone.txt
 (timeout 900 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/r02y_gpu_tests.txt 2>&1; echo "pytest rc=$?" >> gpurun_out/r02y_gpu_tests.txt)
 tail -3 gpurun_out/r02y_gpu_tests.txt; grep -E "^FAILED|^ERROR" gpurun_out/r02y_gpu_tests.txt | head
 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
