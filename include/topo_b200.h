@@ -115,6 +115,19 @@ int topo_embed_sum(topo_handle_t h, const int* ids, const float* word, const flo
 int topo_groupnorm_silu(topo_handle_t h, const void* x, int x_ld, const float* gamma, const float* beta, void* y,
                         int y_ld, int B, int HW, int C, int G, float eps, int apply_silu, float* ws, void* stream);
 int topo_groupnorm_ws_floats(int B, int G);
+/* topo_groupnorm_silu without the `ws` argument, for callers that cannot allocate (CUDA-graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The partial statistics go to a file-scope `static __device__` array of topo_groupnorm_static_max_floats() = 262144
+ * floats (1 MiB, held by every GPU that loads the library until the process exits); the call itself performs no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  Limit: topo_groupnorm_ws_floats(B, G) = B*G*512 must
+ * not exceed that maximum (B * G <= 512, e.g. 16 samples of 32 groups); larger problems fail with TOPO_E_INVAL and a
+ * message that names the limit.  Every call on a GPU shares the one array: calls that overlap on the same GPU (two
+ * streams, two threads) race on it — serialise them, or use topo_groupnorm_silu with one workspace per stream.  Nothing
+ * in the array needs clearing between calls (the statistics pass overwrites every slot the apply pass reads).
+ * Results are bit-identical to topo_groupnorm_silu on the same inputs.                                              */
+int topo_groupnorm_silu_static(topo_handle_t h, const void* x, int x_ld, const float* gamma, const float* beta, void* y,
+                               int y_ld, int B, int HW, int C, int G, float eps, int apply_silu, void* stream);
+int topo_groupnorm_static_max_floats(void);
 
 /* LayerNorm over the last dim of x [M, C] (BasicTransformerBlock.norm1..3, eps 1e-5). */
 int topo_layernorm(topo_handle_t h, const void* x, int x_ld, const float* gamma, const float* beta, void* y, int y_ld,

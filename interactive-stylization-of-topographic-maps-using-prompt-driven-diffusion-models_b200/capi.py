@@ -24,6 +24,7 @@ SYMBOLS = [
     "topo_zeroconv_residual", "topo_timestep_embedding", "topo_ddim_step", "topo_ddim_step_x0", "topo_conv_direct",
     "topo_nchw_f32_to_nhwc_bf16", "topo_nhwc_to_nchw_f32", "topo_upsample2x", "topo_im2col3x3_s2", "topo_im2col3x3_s2_pad", "topo_tile_metrics", "topo_im2col3x3_s1_k64",
     "topo_add_bf16", "topo_tile_to_u8", "topo_tile_to_u8_round", "topo_softmax_rows", "topo_geglu_tile",
+    "topo_groupnorm_silu_static", "topo_groupnorm_static_max_floats",
 ]
 
 
@@ -71,6 +72,8 @@ def load_library(path: str = LIB_PATH) -> C.CDLL:
     lib.topo_embed_sum.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     lib.topo_groupnorm_silu.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp, vp]
     lib.topo_groupnorm_ws_floats.argtypes = [i32, i32]
+    lib.topo_groupnorm_silu_static.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, vp]
+    lib.topo_groupnorm_static_max_floats.argtypes = []
     lib.topo_geglu_tile.argtypes = [i32]
     lib.topo_layernorm.argtypes = [vp, vp, i32, vp, vp, vp, i32, i32, i32, f32, vp]
     lib.topo_zeroconv_residual.argtypes = [vp, vp, i32, vp, vp, f32, vp, i32, vp, i32, i32, i32, i32, vp]

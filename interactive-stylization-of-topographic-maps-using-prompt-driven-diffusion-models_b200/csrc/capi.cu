@@ -162,6 +162,14 @@ using namespace topo;
   } while (0)
 #define ST(s) reinterpret_cast<cudaStream_t>(s)
 
+namespace topo {
+// H_CHECK for entry points that live next to their kernels (topo_ctx is private to this file)
+int handle_check(const topo_ctx* h) {
+  H_CHECK(h);
+  return 0;
+}
+}  // namespace topo
+
 extern "C" {
 
 int topo_version(void) { return TOPO_VERSION; }

@@ -45,6 +45,11 @@ int device_sm_count();
 // name of the kernel (template instance) the calling thread's last dispatch launched: topo_last_kernel() returns it, so the
 // host-side per-launch timing (bench.py's roofline leg) is keyed by the same names an ncu launch list shows
 void note_kernel(const char* fmt, ...);
+}  // namespace topo
+struct topo_ctx;
+namespace topo {
+// null / wrong-architecture handle test of the C ABI (sets the error text); 0 when the handle is usable
+int handle_check(const topo_ctx* h);
 
 // ---------------------------------------------------------------------------------------------
 // device helpers

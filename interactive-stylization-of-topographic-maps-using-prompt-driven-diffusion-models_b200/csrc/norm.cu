@@ -7,6 +7,8 @@
 //   layernorm: one warp per row, the row is held in registers (C <= 2048), exact two-pass variance.
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "topo_b200.h"
 
@@ -471,6 +473,36 @@ int groupnorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
 }
 
 // ------------------------------------------------------------------------------------------------
+// GroupNorm without a caller workspace (topo_groupnorm_silu_static): the per-(sample, slab, group) partial sums of the
+// statistics pass live in this file-scope device array instead of caller memory, so the call allocates nothing.  Every
+// device that loads the library holds GN_STATIC_WS_FLOATS * 4 bytes = 1 MiB until the process exits.  All calls share
+// the array: two calls that overlap on one GPU (different streams) race on it.  Nothing in it has to start at zero —
+// the statistics pass stores (never accumulates into) every slot the apply pass of the same call reads — so the
+// contents a previous call left behind are never observed.
+// ------------------------------------------------------------------------------------------------
+constexpr int GN_STATIC_WS_FLOATS = 1 << 18;
+static __device__ __align__(256) float g_gn_static_ws[GN_STATIC_WS_FLOATS];
+
+// In host code `g_gn_static_ws` is a host-side stand-in, not a device address: resolve it once per device, with that
+// device current, and hand the kernels the resolved pointer.
+static int gn_static_ws_ptr(float** out) {
+  static std::mutex mu;
+  static float* ptr[64] = {nullptr};
+  int dev = 0;
+  TOPO_CUDA(cudaGetDevice(&dev));
+  TOPO_CHECK(dev >= 0 && dev < 64, TOPO_E_INVAL, "groupnorm_static: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptr[dev]) {
+    void* p = nullptr;
+    TOPO_CUDA(cudaGetSymbolAddress(&p, g_gn_static_ws));
+    TOPO_CHECK(p != nullptr, TOPO_E_CUDA, "groupnorm_static: cudaGetSymbolAddress returned a null pointer");
+    ptr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
 // LayerNorm: one warp per row
 // ------------------------------------------------------------------------------------------------
 template <int MAXV>
@@ -651,3 +683,25 @@ int layernorm_dispatch(const void* x, int x_ld, const float* gamma, const float*
 }
 
 }  // namespace topo
+
+extern "C" {
+
+int topo_groupnorm_static_max_floats(void) { return topo::GN_STATIC_WS_FLOATS; }
+
+int topo_groupnorm_silu_static(topo_handle_t h, const void* x, int x_ld, const float* gamma, const float* beta, void* y,
+                               int y_ld, int B, int HW, int C, int G, float eps, int apply_silu, void* stream) {
+  using namespace topo;
+  if (int rc = handle_check(h)) return rc;
+  TOPO_CHECK(x && y && gamma && beta, TOPO_E_INVAL, "topo_groupnorm_silu_static: null argument");
+  TOPO_CHECK(B > 0 && G > 0 && HW > 0, TOPO_E_INVAL, "topo_groupnorm_silu_static: B=%d G=%d HW=%d", B, G, HW);
+  const long long need = (long long)B * G * 2 * GN_MAX_SPLITS;  // = topo_groupnorm_ws_floats(B, G), without the overflow
+  TOPO_CHECK(need <= GN_STATIC_WS_FLOATS, TOPO_E_INVAL,
+             "topo_groupnorm_silu_static: B=%d x G=%d needs %lld scratch floats, the static scratch holds %d (B*G <= %d); "
+             "use topo_groupnorm_silu with a caller workspace",
+             B, G, need, GN_STATIC_WS_FLOATS, GN_STATIC_WS_FLOATS / (2 * GN_MAX_SPLITS));
+  float* ws = nullptr;
+  if (int rc = gn_static_ws_ptr(&ws)) return rc;
+  return groupnorm_dispatch(x, x_ld, gamma, beta, y, y_ld, B, HW, C, G, eps, apply_silu, ws, reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"
