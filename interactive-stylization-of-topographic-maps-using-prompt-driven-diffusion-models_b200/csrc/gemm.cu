@@ -56,6 +56,8 @@ struct alignas(64) GemmParams {
   int taps;          // 1 or 9
   int n_seg, m_tiles, total_tiles;
   int nt_total;   // n tiles over all segments; > 0 selects the n-fastest tile order with contiguous per-CTA chunks
+  int strided;    // with nt_total > 0: keep the n-fastest ids but walk them strided (gridDim.x is a multiple of nt_total, so
+                  // a CTA sees ONE n tile: the resident-W kernel)
   // conv geometry
   int H, W, bw, bh, bb, tiles_w, tiles_h;
 };
@@ -63,22 +65,34 @@ struct alignas(64) GemmParams {
 // PAIR: two CTAs of a cluster run one M = 256 UMMA (cta_group::2); each holds its own 128 x rows and HALF of the W tile
 // (BN / 2 rows), so a stage is 32 KB instead of 48 KB at BN = 256: six stages instead of four, and a third less L2 -> SM
 // traffic per FLOP.
-template <int BN, int RPAD, int STAGES, bool PAIR = false>
+// RESID (short-K projections only, K <= |RESID| * 64): one operand stays RESIDENT in shared memory and the ring carries
+// the other one alone, because these kernels are bound by the L2 -> SM fill (a 128 x 160 x 320 tile pulls 184 KB through
+// the ring for 41 KB of output):
+//   RESID > 0  the CTA's W tile (BN x K) is loaded ONCE; the CTA keeps its n tile for its whole (strided) walk over the row
+//              tiles and streams x only                                            (N = one or two tiles: 64x64-level projections)
+//   RESID < 0  the x tile (128 x K) of a row tile stays while the CTA walks that row tile's n tiles (n-fastest order) and
+//              streams W only                                                      (many n tiles: GEGLU, fused q/k/v)
+template <int BN, int RPAD, int STAGES, bool PAIR = false, int RESID = 0>
 struct GemmSmem {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int W_BYTES = (PAIR ? BN / 2 : BN) * BK * 2;
   static constexpr int LA_BYTES = RPAD * BK * 2;            // LoRA-A tile of a T pre-pass stage: lives in the W slot
-  static constexpr int STAGE_BYTES = A_BYTES + W_BYTES;
+  static constexpr int STAGE_BYTES = RESID > 0 ? A_BYTES : (RESID < 0 ? W_BYTES : A_BYTES + W_BYTES);
+  static constexpr int RES_KB = RESID > 0 ? RESID : -RESID;
+  static constexpr int RES_BYTES = RES_KB * (RESID > 0 ? W_BYTES : A_BYTES);
   static constexpr int LB_BYTES = BN * RPAD * 2;
   static constexpr int T_ONE = BM * RPAD * 2;
   static constexpr int T_BYTES = 2 * T_ONE;                 // two (s T) tiles: group g+1 is converted while group g is in use
-  static constexpr int LB_OFF = STAGES * STAGE_BYTES;
+  static constexpr int RES_OFF = STAGES * STAGE_BYTES;
+  static constexpr int LB_OFF = RES_OFF + RES_BYTES;
   static constexpr int T_OFF = LB_OFF + LB_BYTES;
   static constexpr int STG_OFF = T_OFF + T_BYTES;          // fp32 staging: [32 rows][32 cols] per epilogue warp
   static constexpr int BIAS_OFF = STG_OFF + EPI_WARPS * 32 * 32 * 4;   // 2 x BN floats
   static constexpr int BAR_OFF = BIAS_OFF + 2 * BN * 4;
-  static constexpr int TOTAL = BAR_OFF + 256;              // barriers (the dynamic window itself is 1 KB aligned)
+  static constexpr int TOTAL = BAR_OFF + (RESID ? 384 : 256);   // barriers (the dynamic window itself is 1 KB aligned)
   static_assert(TOTAL <= 232448, "shared memory budget exceeded");
+  static_assert(RESID == 0 || (!PAIR && RPAD == 0), "resident operands: single-CTA, non-LoRA tiles only");
+  static_assert((W_BYTES % 1024) == 0 || RESID == 0, "resident / W-only stages must keep the 1 KB swizzle alignment");
 };
 
 struct TileCoord {
@@ -133,10 +147,11 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
   return c;
 }
 
-template <int BN, int RPAD, int STAGES, bool CONV, bool PAIR = false>
-__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+template <int BN, int RPAD, int STAGES, bool CONV, bool PAIR, int RESID>
+__device__ __forceinline__ void gemm_body(const GemmParams& p) {
   static_assert(!PAIR || RPAD == 0, "the CTA-pair variant has no LoRA side product");
-  using L = GemmSmem<BN, RPAD, STAGES, PAIR>;
+  static_assert(RESID == 0 || !CONV, "resident operands: plain projections only");
+  using L = GemmSmem<BN, RPAD, STAGES, PAIR, RESID>;
   // no static shared memory in this kernel: the dynamic window starts at the CTA's 1 KB-aligned base (SWIZZLE_128B
   // needs it; a violation becomes a launch failure), which saves the 1 KB of slack the fourth BN = 256 stage needs
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -155,6 +170,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   uint64_t* side_full = lb_full + 2;       // main loop (acc + T) finished
   uint64_t* t_ready = lb_full + 3;         // s*T written to smem (128 arrivals)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(lb_full + 4);
+  // resident operand: RESID > 0 one barrier (the W tile landed); RESID < 0 a full / empty pair per x k-block slot
+  uint64_t* res_full = lb_full + 5;        // [RES_KB]
+  uint64_t* res_empty = res_full + L::RES_KB;   // [RES_KB]
+  uint8_t* res_tile = smem + L::RES_OFF;
 
   const int warp = threadIdx.x >> 5;
   // tile walk: strided (m-fastest order) or a contiguous chunk per CTA (n-fastest order)
@@ -165,9 +184,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   const int walker = PAIR ? (int)blockIdx.x / 2 : (int)blockIdx.x;
   const int walk_total = PAIR ? ((p.m_tiles + 1) / 2) * p.nt_total : p.total_tiles;
   const int chunk = (walk_total + walkers - 1) / walkers;
-  const int tile_begin = p.nt_total > 0 ? walker * chunk : walker;
-  const int tile_end = p.nt_total > 0 ? min(walk_total, tile_begin + chunk) : walk_total;
-  const int tile_step = p.nt_total > 0 ? 1 : walkers;
+  const bool chunked = p.nt_total > 0 && !(RESID > 0 && p.strided);
+  const int tile_begin = chunked ? walker * chunk : walker;
+  const int tile_end = chunked ? min(walk_total, tile_begin + chunk) : walk_total;
+  const int tile_step = chunked ? 1 : walkers;
   auto tile_id = [&](int t) { return PAIR ? (2 * (t / p.nt_total) + rank) * p.nt_total + t % p.nt_total : t; };
   const int lane = threadIdx.x & 31;
   const int kc = p.K / BK;
@@ -201,6 +221,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     mbar_init(lb_empty, 1);
     mbar_init(side_full, 1);
     mbar_init(t_ready, 128);
+    if (RESID) {
+      for (int i = 0; i < L::RES_KB; ++i) {
+        mbar_init(&res_full[i], 1);
+        mbar_init(&res_empty[i], 1);
+      }
+    }
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -233,9 +259,40 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         }
       };
+      if (RESID > 0 && tile_begin < tile_end) {
+        // the CTA's W tile, once: all k-blocks on one barrier
+        const TileCoord c0 = tile_coord<BN, CONV>(p, tile_id(tile_begin));
+        mbar_expect_tx(&res_full[0], num_kb * L::W_BYTES);
+        for (int kb = 0; kb < num_kb; ++kb) tma_load_2d(res_tile + kb * L::W_BYTES, &p.seg[c0.seg].tm_w, &res_full[0], kb * BK, c0.n0);
+      }
+      int grp = -1, grp_m0 = -1;   // RESID < 0: row-tile group counter of this CTA (parity of the x slots' barriers)
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
         const GemmSegDev& sg = p.seg[c.seg];
+        if (RESID != 0) {
+          const bool new_group = RESID < 0 && (it == 0 || c.m0 != grp_m0);
+          if (new_group) {
+            ++grp;
+            grp_m0 = c.m0;
+          }
+          for (int kb = 0; kb < num_kb; ++kb) {
+            if (new_group) {                   // slot kb is free once the previous group's last tile has multiplied it
+              mbar_wait(&res_empty[kb], (grp & 1) ^ 1);
+              mbar_expect_tx(&res_full[kb], L::A_BYTES);
+              tma_load_2d(res_tile + kb * L::A_BYTES, &p.tm_x, &res_full[kb], kb * BK, c.m0);
+            }
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint8_t* r_s = smem + stage * L::STAGE_BYTES;
+            mbar_expect_tx(&full[stage], L::STAGE_BYTES);
+            if (RESID > 0) tma_load_2d(r_s, &p.tm_x, &full[stage], kb * BK, c.m0);
+            else tma_load_2d(r_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+          continue;
+        }
         if (RPAD) {
           if (it == 0) load_tpass(c);
           if (tile + tile_step < tile_end) {
@@ -320,12 +377,26 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         }
         umma_commit(side_full);
       };
+      if (RESID > 0 && tile_begin < tile_end) {
+        mbar_wait(&res_full[0], 0);
+        tc_fence_after();
+      }
+      int grp = -1, grp_m0 = -1;
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const int buf = NBUF == 2 ? (it & 1) : 0;
         const uint32_t acc_phase = NBUF == 2 ? ((it >> 1) & 1) : (it & 1);
         const uint32_t tmem_acc = tmem_base + buf * BN;
         // the last N tile of a segment only multiplies the columns that exist (UMMA N is a run-time field, multiple of 16)
         const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
+        bool grp_first = false, grp_last = false;   // RESID < 0: first / last tile of this CTA's row-tile group
+        if (RESID < 0) {
+          grp_first = it == 0 || c.m0 != grp_m0;
+          if (grp_first) {
+            ++grp;
+            grp_m0 = c.m0;
+          }
+          grp_last = tile + tile_step >= tile_end || tile_coord<BN, CONV>(p, tile_id(tile + tile_step)).m0 != c.m0;
+        }
         const int n_left = p.seg[c.seg].N - c.n0;
         const uint32_t n_eff = n_left >= BN ? BN : (PAIR ? ((n_left + 31) & ~31) : ((n_left + 15) & ~15));
         const uint32_t idesc_main = make_idesc_bf16(PAIR ? 2 * BM : BM, n_eff);
@@ -358,8 +429,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t a_s = smem_u32(smem + stage * L::STAGE_BYTES);
-          const uint32_t w_s = a_s + L::A_BYTES;
+          if (RESID < 0 && grp_first) {
+            mbar_wait(&res_full[kb], grp & 1);
+            tc_fence_after();
+          }
+          const uint32_t ring_s = smem_u32(smem + stage * L::STAGE_BYTES);
+          const uint32_t a_s = RESID < 0 ? smem_u32(res_tile + kb * L::A_BYTES) : ring_s;
+          const uint32_t w_s = RESID > 0 ? smem_u32(res_tile + kb * L::W_BYTES) : (RESID < 0 ? ring_s : ring_s + L::A_BYTES);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
@@ -371,6 +447,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
           if (PAIR) umma2_commit(&empty[stage]);   // frees the stage in BOTH CTAs
           else umma_commit(&empty[stage]);
+          if (RESID < 0 && grp_last) umma_commit(&res_empty[kb]);   // the next row tile's x may overwrite slot kb
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -655,6 +732,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   }
 }
 
+template <int BN, int RPAD, int STAGES, bool CONV, bool PAIR = false>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  gemm_body<BN, RPAD, STAGES, CONV, PAIR, 0>(p);
+}
+
+// short-K projections with one operand resident in shared memory (see GemmSmem): RESID > 0 W stays, RESID < 0 x stays
+template <int BN, int STAGES, int RESID>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_resident_kernel(const __grid_constant__ GemmParams p) {
+  gemm_body<BN, 0, STAGES, false, false, RESID>(p);
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -724,6 +812,36 @@ static int launch_gemm(const GemmParams& p, dim3 grid, cudaStream_t st) {
   TOPO_CUDA(cudaGetLastError());
   note_kernel("gemm_kernel<%d, %d, %d, %d, 0>", BN, RPAD, STAGES, (int)CONV);
   return 0;
+}
+
+// Resident-operand launch (gemm_resident_kernel).  RESID > 0: the grid is the largest multiple of the n-tile count that
+// fits the SMs and the n-fastest tile ids are walked strided, so CTA c keeps n tile c % nt_total.  RESID < 0: the regular
+// n-fastest contiguous chunks (the tiles of one row tile are consecutive in a CTA's chunk).
+template <int BN, int STAGES, int RESID>
+static int launch_gemm_res(const GemmParams& p, cudaStream_t st) {
+  using L = GemmSmem<BN, 0, STAGES, false, RESID>;
+  auto kfn = gemm_resident_kernel<BN, STAGES, RESID>;
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kfn), L::TOTAL)) return rc;
+  GemmParams q = p;
+  q.nt_total = 0;
+  for (int i = 0; i < p.n_seg; ++i) q.nt_total += p.seg[i].n_tiles;
+  TOPO_CHECK(p.K / BK <= L::RES_KB, TOPO_E_INVAL, "resident GEMM: K=%d exceeds %d k-blocks", p.K, L::RES_KB);
+  int ctas = sm_count();
+  if (RESID > 0) {
+    q.strided = 1;
+    ctas = (ctas / q.nt_total) * q.nt_total;
+  }
+  if (ctas > p.total_tiles) ctas = p.total_tiles;
+  kfn<<<ctas, GEMM_THREADS, L::TOTAL, st>>>(q);
+  TOPO_CUDA(cudaGetLastError());
+  note_kernel("gemm_resident_kernel<%d, %d, %d>", BN, STAGES, RESID);
+  return 0;
+}
+
+// TOPO_RESIDENT: bit 0 = resident-W projections, bit 1 = resident-x (GEGLU / fused q,k,v); default 3, 0 = off (A/B runs)
+static int resident_mask() {
+  static const int v = [] { const char* e = getenv("TOPO_RESIDENT"); return e ? atoi(e) : 3; }();
+  return v;
 }
 
 // GEGLU column interleave granularity the host must pack with (ops.geglu_interleave): values | gates per N tile.
@@ -864,6 +982,10 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
     for (int i = 0; i < n_seg; ++i) all192 = all192 && segs[i].N % 192 == 0 && segs[i].act == TOPO_ACT_NONE;
     if (all192) BN = 192;
   }
+  // N = 384 (padded-head q projection of the 64x64 level), K <= 320: two 192-wide tiles with W resident
+  if ((resident_mask() & 1) && n_seg == 1 && segs[0].r_pad == 0 && segs[0].act != TOPO_ACT_GEGLU && segs[0].N == 384 && K <= 320 &&
+      (M + BM - 1) / BM >= sm_count())
+    BN = 192;
   GemmParams p;
   memset(&p, 0, sizeof(p));
   uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -898,6 +1020,21 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   dim3 grid(p.total_tiles);
   if (wide320) return launch_gemm_pair<320, 5, false>(p, st);
   if (pair) return launch_gemm_pair<256, 6, false>(p, st);
+  // short-K projections of the 64x64 level: one operand resident in shared memory (see GemmSmem)
+  if (r_pad == 0 && K <= 384 && p.total_tiles >= 2 * sm_count()) {
+    const int kc = K / BK;
+    if ((resident_mask() & 1) && n_seg == 1 && segs[0].act != TOPO_ACT_GEGLU && segs[0].N % BN == 0 && segs[0].N / BN <= 2) {
+      if (BN == 160 && kc <= 5) return launch_gemm_res<160, 5, 5>(p, st);
+      if (BN == 160 && kc == 6) return launch_gemm_res<160, 4, 6>(p, st);
+      if (BN == 192 && kc <= 5) return launch_gemm_res<192, 4, 5>(p, st);
+    }
+    bool plain_or_geglu = true;
+    for (int i = 0; i < n_seg; ++i) plain_or_geglu = plain_or_geglu && segs[i].N % BN == 0;
+    if ((resident_mask() & 2) && kc <= 5 && plain_or_geglu && p.total_tiles / p.m_tiles >= 4) {
+      if (BN == 256) return launch_gemm_res<256, 3, -5>(p, st);
+      if (BN == 192) return launch_gemm_res<192, 4, -5>(p, st);
+    }
+  }
   if (r_pad == 16) {
     if (BN == 192) return launch_gemm<192, 16, 4, false>(p, grid, st);
     if (BN == 160) return launch_gemm<160, 16, 5, false>(p, grid, st);

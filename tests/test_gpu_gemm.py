@@ -154,5 +154,57 @@ def test_fused_qkv_plain_192_wide_tiles():
     Ws = [rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16) for i in range(3)]
     segs = [capi.make_linear(W, out, N, out_ld=3 * N, out_col=i * N) for i, W in enumerate(Ws)]
     ops.lora_linear_raw(x, M, K, K, segs)
-    assert capi.last_kernel() == "gemm_kernel<192, 0, 4, 0, 0>", capi.last_kernel()
+    assert capi.last_kernel() in ("gemm_resident_kernel<192, 4, -5>", "gemm_kernel<192, 0, 4, 0, 0>"), capi.last_kernel()
     assert_close(out, torch.cat([x.float() @ W.float().t() for W in Ws], 1), TOL, "fused qkv, 192-wide tiles")
+
+
+# ---- short-K projections with one operand resident in shared memory (gemm_resident_kernel) -------------------------------
+@pytest.mark.parametrize("M,K,N,res,kernel", [
+    (148 * 128 * 2 + 77, 320, 320, True, "gemm_resident_kernel<160, 5, 5>"),     # attention out-projection / proj_out, 64x64 level
+    (148 * 128 + 1, 384, 320, True, "gemm_resident_kernel<160, 4, 6>"),          # out-projection from padded heads (8 x 48)
+    (148 * 128 + 130, 256, 320, False, "gemm_resident_kernel<160, 5, 5>"),       # fewer k-blocks than slots
+    (148 * 128 + 64, 320, 384, False, "gemm_resident_kernel<192, 4, 5>"),        # padded-head q projection
+    (148 * 128 * 2, 320, 160, True, "gemm_resident_kernel<160, 5, 5>"),          # one n tile: W fully resident
+])
+def test_resident_w_projection(M, K, N, res, kernel):
+    """W tile loaded once per CTA, x streamed; every CTA keeps one n tile over a strided row-tile walk (ragged M tail,
+    bias, residual).  Also run twice: the second launch must not depend on anything the first left in shared memory."""
+    from topo_b200 import capi
+    ops = _ops()
+    x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
+    b = rnd(N, seed=3)
+    rs = rnd(M, N, seed=4).to(BF16) if res else None
+    ref = x.float() @ W.float().t() + b + (rs.float() if res else 0)
+    for _ in range(2):
+        y = ops.linear(x, W, b, res=rs)
+        assert capi.last_kernel() == kernel, capi.last_kernel()
+        assert_close(y, ref, TOL, f"resident-W M{M} K{K} N{N}")
+
+
+def test_resident_x_geglu():
+    """GEGLU of the 64x64 level (N = 2560, K = 320): the x tile of a row tile stays in shared memory while the CTA walks
+    that row tile's ten n tiles; chunk boundaries fall inside row tiles (1480 + 3 row tiles over 148 CTAs)."""
+    from topo_b200 import capi
+    ops = _ops()
+    M, K, inner = 148 * 128 + 300, 320, 1280
+    x, W, b = rnd(M, K, seed=1).to(BF16), rnd(2 * inner, K, seed=2, scale=K ** -0.5).to(BF16), rnd(2 * inner, seed=3)
+    h = x.float() @ W.float().t() + b
+    a, g = h.chunk(2, -1)
+    for _ in range(2):
+        y = ops.linear(x, W, b, act=ops.ACT_GEGLU)
+        assert capi.last_kernel() == "gemm_resident_kernel<256, 3, -5>", capi.last_kernel()
+        assert_close(y, a * F.gelu(g), TOL, "resident-x GEGLU")
+
+
+def test_resident_x_fused_qkv_with_bias_and_ragged_tail():
+    from topo_b200 import capi
+    ops = _ops()
+    M, K, N = 148 * 128 + 129, 320, 384
+    x = rnd(M, K, seed=1).to(BF16)
+    out = torch.zeros(M, 3 * N, dtype=BF16, device="cuda")
+    Ws = [rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16) for i in range(3)]
+    bs = [rnd(N, seed=20 + i) for i in range(3)]
+    segs = [capi.make_linear(W, out, N, bias=b, out_ld=3 * N, out_col=i * N) for i, (W, b) in enumerate(zip(Ws, bs))]
+    ops.lora_linear_raw(x, M, K, K, segs)
+    assert capi.last_kernel() == "gemm_resident_kernel<192, 4, -5>", capi.last_kernel()
+    assert_close(out, torch.cat([x.float() @ W.float().t() + b for W, b in zip(Ws, bs)], 1), TOL, "resident-x fused qkv")

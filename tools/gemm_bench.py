@@ -24,7 +24,7 @@ def timeit(fn, flops, nbytes, name):
         e0.record(); fn(); e1.record(); torch.cuda.synchronize()
         ts.append(e0.elapsed_time(e1))
     ms = sorted(ts)[len(ts) // 2]
-    print(f"{name:52s} {ms*1e3:8.1f} us  {flops/1e9/ms:7.1f} TF/s  {nbytes/1e6/ms:7.1f} GB/s", flush=True)
+    print(f"{name:52s} {ms*1e3:8.1f} us  {flops/1e9/ms:7.1f} TF/s  {nbytes/1e6/ms:7.1f} GB/s  {capi.last_kernel()}", flush=True)
 
 
 def gemm_case(M, N, K, res=False, act=0, r=0):
@@ -64,7 +64,17 @@ def attn_case(B, N, Nk, d, heads=8):
            f"attn B{B} N{N} Nk{Nk} d{d}")
 
 
+def qkv_case(M, N, K):
+    x = torch.randn(M, K, device="cuda").to(BF)
+    Ws = [(torch.randn(N, K, device="cuda") * K ** -0.5).to(BF) for _ in range(3)]
+    out = torch.empty(M, 3 * N, device="cuda", dtype=BF)
+    segs = [capi.make_linear(W, out, N, out_ld=3 * N, out_col=i * N) for i, W in enumerate(Ws)]
+    timeit(lambda: ops.lora_linear_raw(x, M, K, K, segs), 6.0 * M * N * K, 2.0 * (M * K + 3 * N * K + 3 * M * N), f"qkv  M{M} N3x{N} K{K}")
+
+
 Be = 38
+gemm_case(Be * 4096, 384, 320)
+qkv_case(Be * 4096, 384, 320)
 gemm_case(Be * 4096, 320, 320, res=True)
 gemm_case(Be * 4096, 320, 320)
 gemm_case(Be * 4096, 320, 384, res=True)
