@@ -28,7 +28,7 @@ namespace topo {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int EPI_WARPS = 8;
+constexpr int EPI_WARPS = 16;   // four per TMEM lane quadrant
 constexpr int EPI_THREADS = EPI_WARPS * 32;
 constexpr int GEMM_THREADS = 64 + EPI_THREADS;
 constexpr int MAX_SEG = 3;
@@ -86,8 +86,8 @@ struct GemmSmem {
   static constexpr int RES_OFF = STAGES * STAGE_BYTES;
   static constexpr int LB_OFF = RES_OFF + RES_BYTES;
   static constexpr int T_OFF = LB_OFF + LB_BYTES;
-  static constexpr int STG_OFF = T_OFF + T_BYTES;          // fp32 staging: [32 rows][32 cols] per epilogue warp
-  static constexpr int BIAS_OFF = STG_OFF + EPI_WARPS * 32 * 32 * 4;   // 2 x BN floats
+  static constexpr int STG_OFF = T_OFF + T_BYTES;          // bf16 staging: [32 rows][32 cols] per epilogue warp
+  static constexpr int BIAS_OFF = STG_OFF + EPI_WARPS * 32 * 32 * 2;   // 2 x BN floats
   static constexpr int BAR_OFF = BIAS_OFF + 2 * BN * 4;
   static constexpr int TOTAL = BAR_OFF + (RESID ? 384 : 256);   // barriers (the dynamic window itself is 1 KB aligned)
   static_assert(TOTAL <= 232448, "shared memory budget exceeded");
@@ -158,7 +158,7 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* lb_tile = smem + L::LB_OFF;
   uint8_t* t_tile = smem + L::T_OFF;
-  float* stage_f = reinterpret_cast<float*>(smem + L::STG_OFF);
+  uint8_t* stage_b = smem + L::STG_OFF;
   float* sbias_all = reinterpret_cast<float*>(smem + L::BIAS_OFF);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
   uint64_t* full = bars;                   // [STAGES] TMA landed
@@ -241,7 +241,17 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // The WHOLE warp walks the loop (warp-uniform control flow keeps coordinates, stage addresses and barrier addresses in
+    // uniform registers); one elected lane issues.  With the loop under `lane == 0` every operand of a TMA / UMMA instruction
+    // was computed in vector registers and moved over with R2UR: ~125 instructions per k-block in the issuer, 3-4x the
+    // duration of the four UMMAs they issue (profiles/r02m_ncu_source_issuer.txt).
+    {
+      const bool lead = elect_one();
+      auto expect = [&](uint64_t* b, uint32_t bytes) { if (lead) mbar_expect_tx(b, bytes); };
+      auto ld2 = [&](void* d, const CUtensorMap* mp, uint64_t* b, int c0, int c1) { if (lead) tma_load_2d(d, mp, b, c0, c1); };
+      auto ld4 = [&](void* d, const CUtensorMap* mp, uint64_t* b, int c0, int c1, int c2, int c3) { if (lead) tma_load_4d(d, mp, b, c0, c1, c2, c3); };
+      auto ld2p = [&](void* d, const CUtensorMap* mp, uint32_t b, int c0, int c1) { if (lead) tma2_load_2d(d, mp, b, c0, c1); };
+      auto ld4p = [&](void* d, const CUtensorMap* mp, uint32_t b, int c0, int c1, int c2, int c3) { if (lead) tma2_load_4d(d, mp, b, c0, c1, c2, c3); };
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -250,9 +260,9 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* a_s = smem + stage * L::STAGE_BYTES;
-          mbar_expect_tx(&full[stage], L::A_BYTES + L::LA_BYTES);
-          tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, g.m0);
-          tma_load_2d(a_s + L::A_BYTES, &p.seg[g.seg].tm_la, &full[stage], kb * BK, 0);
+          expect(&full[stage], L::A_BYTES + L::LA_BYTES);
+          ld2(a_s, &p.tm_x, &full[stage], kb * BK, g.m0);
+          ld2(a_s + L::A_BYTES, &p.seg[g.seg].tm_la, &full[stage], kb * BK, 0);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -262,8 +272,8 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
       if (RESID > 0 && tile_begin < tile_end) {
         // the CTA's W tile, once: all k-blocks on one barrier
         const TileCoord c0 = tile_coord<BN, CONV>(p, tile_id(tile_begin));
-        mbar_expect_tx(&res_full[0], num_kb * L::W_BYTES);
-        for (int kb = 0; kb < num_kb; ++kb) tma_load_2d(res_tile + kb * L::W_BYTES, &p.seg[c0.seg].tm_w, &res_full[0], kb * BK, c0.n0);
+        expect(&res_full[0], num_kb * L::W_BYTES);
+        for (int kb = 0; kb < num_kb; ++kb) ld2(res_tile + kb * L::W_BYTES, &p.seg[c0.seg].tm_w, &res_full[0], kb * BK, c0.n0);
       }
       int grp = -1, grp_m0 = -1;   // RESID < 0: row-tile group counter of this CTA (parity of the x slots' barriers)
       for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
@@ -278,14 +288,14 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           for (int kb = 0; kb < num_kb; ++kb) {
             if (new_group) {                   // slot kb is free once the previous group's last tile has multiplied it
               mbar_wait(&res_empty[kb], (grp & 1) ^ 1);
-              mbar_expect_tx(&res_full[kb], L::A_BYTES);
-              tma_load_2d(res_tile + kb * L::A_BYTES, &p.tm_x, &res_full[kb], kb * BK, c.m0);
+              expect(&res_full[kb], L::A_BYTES);
+              ld2(res_tile + kb * L::A_BYTES, &p.tm_x, &res_full[kb], kb * BK, c.m0);
             }
             mbar_wait(&empty[stage], phase ^ 1);
             uint8_t* r_s = smem + stage * L::STAGE_BYTES;
-            mbar_expect_tx(&full[stage], L::STAGE_BYTES);
-            if (RESID > 0) tma_load_2d(r_s, &p.tm_x, &full[stage], kb * BK, c.m0);
-            else tma_load_2d(r_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
+            expect(&full[stage], L::STAGE_BYTES);
+            if (RESID > 0) ld2(r_s, &p.tm_x, &full[stage], kb * BK, c.m0);
+            else ld2(r_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1;
@@ -300,8 +310,8 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
             if (cn.m0 != c.m0 || cn.seg != c.seg) load_tpass(cn);
           }
           mbar_wait(lb_empty, (it & 1) ^ 1);  // previous tile's LoRA-up MMA is done with lb_tile
-          mbar_expect_tx(lb_full, L::LB_BYTES);
-          tma_load_2d(lb_tile, &sg.tm_lb, lb_full, 0, c.n0);
+          expect(lb_full, L::LB_BYTES);
+          ld2(lb_tile, &sg.tm_lb, lb_full, 0, c.n0);
         }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -309,7 +319,7 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           uint8_t* w_s = a_s + L::A_BYTES;
           if (PAIR) {
             // both CTAs' bytes are credited to the LEADER's full barrier (the only one the MMA issuer waits on)
-            if (rank == 0) mbar_expect_tx(&full[stage], 2 * L::STAGE_BYTES);
+            if (rank == 0) expect(&full[stage], 2 * L::STAGE_BYTES);
             const uint32_t fb = leader_bar(&full[stage]);
             const int n_left = sg.N - c.n0;
             const int n_eff = n_left >= BN ? BN : ((n_left + 31) & ~31);
@@ -317,15 +327,15 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
               const int tap = kb / kc;
               const int c0 = (kb - tap * kc) * BK;
               const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-              tma2_load_4d(a_s, &p.tm_x, fb, c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
+              ld4p(a_s, &p.tm_x, fb, c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
             } else {
-              tma2_load_2d(a_s, &p.tm_x, fb, kb * BK, c.m0);
+              ld2p(a_s, &p.tm_x, fb, kb * BK, c.m0);
             }
             if constexpr (BN == 320) {   // rows [rank*128, +128) of the 256-wide part, rows [256 + rank*32, +32) of the 64-wide part
-              tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * 128);
-              tma2_load_2d(w_s + 128 * BK * 2, &sg.tm_w2, fb, kb * BK, c.n0 + 256 + rank * 32);
+              ld2p(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * 128);
+              ld2p(w_s + 128 * BK * 2, &sg.tm_w2, fb, kb * BK, c.n0 + 256 + rank * 32);
             } else {
-              tma2_load_2d(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * (n_eff / 2));  // this CTA's half of the W rows
+              ld2p(w_s, &sg.tm_w, fb, kb * BK, c.n0 + rank * (n_eff / 2));  // this CTA's half of the W rows
             }
             if (++stage == STAGES) {
               stage = 0;
@@ -333,16 +343,16 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
             }
             continue;
           }
-          mbar_expect_tx(&full[stage], L::STAGE_BYTES);
+          expect(&full[stage], L::STAGE_BYTES);
           if (CONV) {
             const int tap = kb / kc;
             const int c0 = (kb - tap * kc) * BK;
             const int dy = tap / 3 - 1, dx = tap % 3 - 1;
-            tma_load_4d(a_s, &p.tm_x, &full[stage], c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
+            ld4(a_s, &p.tm_x, &full[stage], c0, c.cw0 + dx, c.ch0 + dy, c.cb0);
           } else {
-            tma_load_2d(a_s, &p.tm_x, &full[stage], kb * BK, c.m0);
+            ld2(a_s, &p.tm_x, &full[stage], kb * BK, c.m0);
           }
-          tma_load_2d(w_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
+          ld2(w_s, &sg.tm_w, &full[stage], kb * BK, c.n0);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -352,7 +362,12 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (PAIR: the leader CTA issues for both) =====================
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {   // whole warp, warp-uniform (see the producer); one elected lane issues
+      const bool lead = elect_one();
+      auto mma = [&](uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) { if (lead) umma_bf16(d, a, b, id, acc); };
+      auto mma2 = [&](uint32_t d, uint64_t a, uint64_t b, uint32_t id, uint32_t acc) { if (lead) umma2_bf16(d, a, b, id, acc); };
+      auto commit = [&](uint64_t* b) { if (lead) umma_commit(b); };
+      auto commit2 = [&](uint64_t* b) { if (lead) umma2_commit(b); };
       constexpr uint32_t idesc_side = make_idesc_bf16(BM, RPAD ? RPAD : 16);
       int stage = 0;
       uint32_t phase = 0;
@@ -368,14 +383,14 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           const uint32_t la_s = a_s + L::A_BYTES;
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k)
-            umma_bf16(tmem_t, kmajor_desc(a_s + k * 32, 128), kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
-          umma_commit(&empty[stage]);
+            mma(tmem_t, kmajor_desc(a_s + k * 32, 128), kmajor_desc(la_s + k * 32, 128), idesc_side, (kb | k) != 0);
+          commit(&empty[stage]);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(side_full);
+        commit(side_full);
       };
       if (RESID > 0 && tile_begin < tile_end) {
         mbar_wait(&res_full[0], 0);
@@ -423,8 +438,8 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           const uint32_t lb_s = smem_u32(lb_tile);
 #pragma unroll
           for (int k = 0; k < RPAD / 16; ++k)
-            umma_bf16(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, k != 0);
-          umma_commit(lb_empty);
+            mma(tmem_acc, kmajor_desc(t_s + k * 32, RPAD * 2), kmajor_desc(lb_s + k * 32, RPAD * 2), idesc_main, k != 0);
+          commit(lb_empty);
         }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
@@ -440,26 +455,26 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t ad = kmajor_desc(a_s + k * 32, 128);
             if constexpr (BN == 320) {
-              umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), make_idesc_bf16(2 * BM, 256), (kb | k) != 0);
-              umma2_bf16(tmem_acc + 256, ad, kmajor_desc(w_s + 128 * BK * 2 + k * 32, 128), make_idesc_bf16(2 * BM, 64), (kb | k) != 0);
-            } else if (PAIR) umma2_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
-            else umma_bf16(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, RPAD ? 1u : (uint32_t)((kb | k) != 0));
+              mma2(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), make_idesc_bf16(2 * BM, 256), (kb | k) != 0);
+              mma2(tmem_acc + 256, ad, kmajor_desc(w_s + 128 * BK * 2 + k * 32, 128), make_idesc_bf16(2 * BM, 64), (kb | k) != 0);
+            } else if (PAIR) mma2(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, (kb | k) != 0);
+            else mma(tmem_acc, ad, kmajor_desc(w_s + k * 32, 128), idesc_main, RPAD ? 1u : (uint32_t)((kb | k) != 0));
           }
-          if (PAIR) umma2_commit(&empty[stage]);   // frees the stage in BOTH CTAs
-          else umma_commit(&empty[stage]);
-          if (RESID < 0 && grp_last) umma_commit(&res_empty[kb]);   // the next row tile's x may overwrite slot kb
+          if (PAIR) commit2(&empty[stage]);   // frees the stage in BOTH CTAs
+          else commit(&empty[stage]);
+          if (RESID < 0 && grp_last) commit(&res_empty[kb]);   // the next row tile's x may overwrite slot kb
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        if (PAIR) umma2_commit(&tfull[buf]);
-        else umma_commit(&tfull[buf]);
+        if (PAIR) commit2(&tfull[buf]);
+        else commit(&tfull[buf]);
         if (next_group) ++g_cur;
       }
     }
   } else {
-    // ===================== epilogue (8 warps; TMEM lane quadrant = warp & 3, column half = (warp - 2) >> 2) =====
+    // ===================== epilogue (16 warps; TMEM lane quadrant = warp & 3, column group hsel = (warp - 2) >> 2) =====
     const int q = warp & 3;
     const int hsel = (warp - 2) >> 2;
     const int et = threadIdx.x - 64;
@@ -515,59 +530,60 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
         }
       }
 
-      // ---- the warp owns rows [q*32, +32) x output columns [hsel*colsw, +colsw) of the tile and walks them in
-      //      32-column chunks: phase A (row per thread: TMEM -> registers -> bias/activation -> fp32 staging, 4 KB per
-      //      warp, 16-byte units XOR-swizzled with row&7) then phase B (8 lanes per row, 4 rows per instruction, all 8
-      //      row-groups in flight: residual loads and stores are full 128-byte lines).  Branches on the tile-uniform
-      //      epilogue flavour are hoisted out of the per-column loops.
+      // ---- the warp owns rows [q*32, +32) of the tile and every NH-th 32-column output chunk (c32 = hsel, hsel + NH, ...:
+      //      a narrow N-tail tile still spreads over the warps).  Per chunk, ROW PER THREAD: TMEM -> registers -> bias /
+      //      per-sample bias / activation / alpha -> + residual (the thread's own 64 bytes of its row, fetched one chunk
+      //      ahead) -> bf16 -> a 2 KB per-warp staging tile (16-byte units XOR-swizzled with (row >> 1) & 3, conflict
+      //      free both ways); then 4 lanes per row, 8 rows per instruction: 16-byte loads from the staging tile, 16-byte
+      //      global stores (64 contiguous bytes per row).  fp32 outputs (rare: eps, VAE image, the ResBlock embedding
+      //      table) and chunks that are not 16-byte aligned or not fully inside N go out row per thread.
+      constexpr int NH = EPI_WARPS / 4;
       const int m = c.m0 + row;
       const bool row_ok = m < p.M;
       const bool geglu = sg.act == TOPO_ACT_GEGLU;
       const int NC = geglu ? BN / 2 : BN;        // output columns this tile produces
       const int out_n0 = geglu ? c.n0 / 2 : c.n0;
       const int out_N = geglu ? sg.N / 2 : sg.N;
-      // the tile's valid 32-column output chunks are dealt out ALTERNATELY to the two warps that share a TMEM lane
-      // quadrant (c32 = hsel, hsel + 2, ...), so a narrow N-tail tile still keeps all eight warps busy
       int valid_cols = out_N - out_n0;
       valid_cols = valid_cols < 0 ? 0 : (valid_cols > NC ? NC : valid_cols);
-      const int n_my = (((valid_cols + 31) >> 5) - hsel + 1) >> 1;
+      const int nchunks = (valid_cols + 31) >> 5;
+      const int n_my = nchunks > hsel ? (nchunks - hsel + NH - 1) / NH : 0;
       const float alpha = sg.alpha;
       const float* rb = (sg.rowbias && row_ok) ? sg.rowbias + (size_t)(m / sg.rows_per_group) * sg.rowbias_ld : nullptr;
-      const bool plain = (rb == nullptr) && sg.act == TOPO_ACT_NONE;
+      const bool plain = (sg.rowbias == nullptr) && sg.act == TOPO_ACT_NONE;
       const bool silu = sg.act == TOPO_ACT_SILU;
       const bool gelu = sg.act == TOPO_ACT_GELU;   // BERT intermediate (exact erf form, transformers "gelu")
       const bool relu = sg.act == TOPO_ACT_RELU;   // text adapter MLP
-      const bool vec_ok = ((sg.out_ld | sg.out_col | out_N) & 3) == 0 && (!sg.res || ((sg.res_ld | sg.res_col) & 3) == 0);
-      float* wstage = stage_f + (warp - 2) * (32 * 32);     // this warp's [32 rows][32 cols] fp32 staging
-      float* srow = wstage + lane * 32;
-      const int sub = lane >> 3;                 // phase B: row within a 4-row group
-      const int unit = lane & 7;                 // phase B: 16-byte unit (4 columns) within the 32-column chunk
-      const int rows_left = p.M - (c.m0 + q * 32 + sub);
-      // residual rows are prefetched ONE CHUNK AHEAD (the first chunk before the accumulator is even complete): the
-      // short-K projections were bound by the serial TMEM-load -> staging -> LDG -> STG latency chain of each chunk
-      const bool res_vec = vec_ok && sg.res != nullptr;
-      const bf16* res_row0 = res_vec ? sg.res + (size_t)(c.m0 + q * 32 + sub) * sg.res_ld + sg.res_col : nullptr;
-      const size_t res_step4 = (size_t)4 * sg.res_ld;
-      auto load_res = [&](int chn, uint2 (&dst)[8]) {
+      const bool has_res = sg.res != nullptr;
+      // 16-byte paths need 8-element alignment of every leading dimension / column offset involved
+      const bool vec8 = !sg.out_fp32 && ((sg.out_ld | sg.out_col) & 7) == 0 && (!has_res || ((sg.res_ld | sg.res_col) & 7) == 0);
+      const bool full_rows = c.m0 + BM <= p.M;
+      uint8_t* wstage = stage_b + (warp - 2) * 2048;        // this warp's [32 rows][32 cols] bf16 staging
+      const uint32_t sw_a = (static_cast<uint32_t>(lane) >> 1) & 3u;   // phase A: this thread's row is `lane`
+      uint8_t* srow = wstage + lane * 64;
+      const int brow = lane >> 2;                // phase B: row within an 8-row group
+      const uint32_t bunit = lane & 3;           // phase B: 16-byte unit (8 columns) within the chunk
+      const bf16* res_row = (has_res && row_ok) ? sg.res + (size_t)m * sg.res_ld + sg.res_col : nullptr;
+      // residual of the thread's row: chunk ch + 1 is fetched while chunk ch is processed (the first one before the
+      // accumulator is even complete)
+      auto load_res = [&](int chn, uint4 (&dst)[4]) {
+        const int nn = out_n0 + (hsel + NH * chn) * 32;
+        if (vec8 && res_row != nullptr && chn < n_my && nn + 32 <= out_N) {
+          const uint4* src = reinterpret_cast<const uint4*>(res_row + nn);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) dst[k] = make_uint2(0u, 0u);
-        const int nn = out_n0 + (hsel + 2 * chn) * 32 + unit * 4;
-        if (res_vec && chn < n_my && nn < out_N) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k)
-            if (k * 4 < rows_left) dst[k] = __ldg(reinterpret_cast<const uint2*>(res_row0 + nn + k * res_step4));
+          for (int k = 0; k < 4; ++k) dst[k] = __ldg(src + k);
         }
       };
-      uint2 rnext[8];
-      load_res(0, rnext);
+      uint4 rnext[4];
+      if (has_res) load_res(0, rnext);
       // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
-      // column half write identical values to identical addresses; a slot of parity `buf` is rewritten only after
+      // column group write identical values to identical addresses; a slot of parity `buf` is rewritten only after
       // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
-      constexpr int MAXJ = (BN / 32 + 1) / 2;
+      constexpr int MAXJ = (BN / 32 + NH - 1) / NH;
       float bpre[MAXJ], gpre[MAXJ];
 #pragma unroll
       for (int j = 0; j < MAXJ; ++j) {
-        const int col = (hsel + 2 * j) * 32 + lane;
+        const int col = (hsel + NH * j) * 32 + lane;
         const int nb = c.n0 + col, ng = c.n0 + BN / 2 + col;
         bpre[j] = (sg.bias && j < n_my && nb < sg.N) ? __ldg(sg.bias + nb) : 0.f;
         gpre[j] = (geglu && sg.bias && j < n_my && ng < sg.N) ? __ldg(sg.bias + ng) : 0.f;
@@ -583,47 +599,52 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
 #pragma unroll
       for (int j = 0; j < MAXJ; ++j) {
         if (j < n_my) {
-          sbias[(hsel + 2 * j) * 32 + lane] = bpre[j];
-          if (geglu) sbias[BN / 2 + (hsel + 2 * j) * 32 + lane] = gpre[j];
+          sbias[(hsel + NH * j) * 32 + lane] = bpre[j];
+          if (geglu) sbias[BN / 2 + (hsel + NH * j) * 32 + lane] = gpre[j];
         }
       }
       __syncwarp();
       float v[32];
-      tmem_ld32(tmem_acc + lane_addr + hsel * 32, v);   // chunk j+1 is fetched under phase B of chunk j
+      tmem_ld32(tmem_acc + lane_addr + hsel * 32, v);   // chunk ch+1 is fetched under the stores of chunk ch
 #pragma unroll 1
       for (int ch = 0; ch < n_my; ++ch) {
-        const int c32 = hsel + 2 * ch;           // 32-column chunk index among the tile's OUTPUT columns
+        const int c32 = hsel + NH * ch;          // 32-column chunk index among the tile's OUTPUT columns
+        const int nb = out_n0 + c32 * 32;        // first output column of the chunk
         if (geglu) {
-          float g[32];
-          tmem_ld32(tmem_acc + lane_addr + BN / 2 + c32 * 32, g);
-          tmem_ld_wait32(v);
-          tmem_ld_wait32(g);
-          const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32);
-          const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32);
-#pragma unroll
+          // gates in two 16-column halves (register budget: 18 warps leave 112 registers per thread)
           const float2 al2 = make_float2(alpha, alpha);
-          for (int u = 0; u < 8; ++u) {   // packed FP32x2 throughout: the GEGLU epilogue is issue bound (profiles/r01e_geglu.md)
-            const float4 a4 = ba[u], g4 = bg[u];
-            const float2 ge0 = gelu_erf2(fadd2(make_float2(g[4 * u + 0], g[4 * u + 1]), make_float2(g4.x, g4.y)));
-            const float2 ge1 = gelu_erf2(fadd2(make_float2(g[4 * u + 2], g[4 * u + 3]), make_float2(g4.z, g4.w)));
-            const float2 o0 = fmul2(fmul2(fadd2(make_float2(v[4 * u + 0], v[4 * u + 1]), make_float2(a4.x, a4.y)), ge0), al2);
-            const float2 o1 = fmul2(fmul2(fadd2(make_float2(v[4 * u + 2], v[4 * u + 3]), make_float2(a4.z, a4.w)), ge1), al2);
-            v[4 * u + 0] = o0.x; v[4 * u + 1] = o0.y; v[4 * u + 2] = o1.x; v[4 * u + 3] = o1.y;
+          tmem_ld_wait32(v);
+#pragma unroll
+          for (int hf = 0; hf < 2; ++hf) {
+            float g[16];
+            tmem_ld16(tmem_acc + lane_addr + BN / 2 + c32 * 32 + hf * 16, g);
+            tmem_ld_wait();
+            const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32 + hf * 16);
+            const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32 + hf * 16);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {   // packed FP32x2 throughout: the GEGLU epilogue is issue bound (profiles/r01e_geglu.md)
+              const float4 a4 = ba[u], g4 = bg[u];
+              float* vv = v + hf * 16 + 4 * u;
+              const float2 ge0 = gelu_erf2(fadd2(make_float2(g[4 * u + 0], g[4 * u + 1]), make_float2(g4.x, g4.y)));
+              const float2 ge1 = gelu_erf2(fadd2(make_float2(g[4 * u + 2], g[4 * u + 3]), make_float2(g4.z, g4.w)));
+              const float2 o0 = fmul2(fmul2(fadd2(make_float2(vv[0], vv[1]), make_float2(a4.x, a4.y)), ge0), al2);
+              const float2 o1 = fmul2(fmul2(fadd2(make_float2(vv[2], vv[3]), make_float2(a4.z, a4.w)), ge1), al2);
+              vv[0] = o0.x; vv[1] = o0.y; vv[2] = o1.x; vv[3] = o1.y;
+            }
           }
         } else {
           tmem_ld_wait32(v);
           const float4* b4 = reinterpret_cast<const float4*>(sbias + c32 * 32);
           if (plain) {
+            const float2 al2 = make_float2(alpha, alpha);
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
               const float4 bb = b4[u];
-              v[4 * u] = (v[4 * u] + bb.x) * alpha;
-              v[4 * u + 1] = (v[4 * u + 1] + bb.y) * alpha;
-              v[4 * u + 2] = (v[4 * u + 2] + bb.z) * alpha;
-              v[4 * u + 3] = (v[4 * u + 3] + bb.w) * alpha;
+              const float2 o0 = fmul2(fadd2(make_float2(v[4 * u], v[4 * u + 1]), make_float2(bb.x, bb.y)), al2);
+              const float2 o1 = fmul2(fadd2(make_float2(v[4 * u + 2], v[4 * u + 3]), make_float2(bb.z, bb.w)), al2);
+              v[4 * u] = o0.x; v[4 * u + 1] = o0.y; v[4 * u + 2] = o1.x; v[4 * u + 3] = o1.y;
             }
           } else {
-            const int nb = out_n0 + c32 * 32;
             const bool rb_vec = rb && ((reinterpret_cast<uintptr_t>(rb + nb) & 15) == 0) && nb + 32 <= out_N;
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
@@ -654,69 +675,83 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
         }
         if (ch == n_my - 1) {
           tc_fence_before();
-          tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+2 into it
+          tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+NBUF into it
         }
+        const bool chunk_vec = vec8 && nb + 32 <= out_N;
+        if (chunk_vec) {
+          if (has_res) {
+            uint4 rr[4];
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-          *reinterpret_cast<float4*>(srow + ((u ^ (lane & 7)) << 2)) = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
-        if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + 2) * 32, v);
-        __syncwarp();
-
-        const int n = out_n0 + c32 * 32 + unit * 4;
-        uint2 rr[8];
+            for (int k = 0; k < 4; ++k) rr[k] = rnext[k];
+            load_res(ch + 1, rnext);
+            if (row_ok) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) rr[k] = rnext[k];
-        load_res(ch + 1, rnext);
-        if (vec_ok) {
-          if (n < out_N) {
-            const size_t row0 = (size_t)(c.m0 + q * 32 + sub);
-            const size_t out_step = (size_t)4 * sg.out_ld;
-            const size_t out_off = row0 * sg.out_ld + sg.out_col + n;
-            float4 f[8];
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t w4[4] = {rr[k].x, rr[k].y, rr[k].z, rr[k].w};
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-              const int r = k * 4 + sub;         // row within the warp's 32
-              f[k] = *reinterpret_cast<const float4*>(wstage + r * 32 + ((unit ^ (r & 7)) << 2));
-            }
-            if (sg.out_fp32) {
-              float* op = reinterpret_cast<float*>(sg.out) + out_off;
-#pragma unroll
-              for (int k = 0; k < 8; ++k)
-                if (k * 4 < rows_left)
-                  *reinterpret_cast<float4*>(op + k * out_step) =
-                      make_float4(f[k].x + bf16lo(rr[k].x), f[k].y + bf16hi(rr[k].x), f[k].z + bf16lo(rr[k].y), f[k].w + bf16hi(rr[k].y));
-            } else {
-              bf16* op = reinterpret_cast<bf16*>(sg.out) + out_off;
-#pragma unroll
-              for (int k = 0; k < 8; ++k)
-                if (k * 4 < rows_left) {
-                  uint2 o;
-                  o.x = pack_bf16x2(f[k].x + bf16lo(rr[k].x), f[k].y + bf16hi(rr[k].x));
-                  o.y = pack_bf16x2(f[k].z + bf16lo(rr[k].y), f[k].w + bf16hi(rr[k].y));
-                  *reinterpret_cast<uint2*>(op + k * out_step) = o;
+                for (int j = 0; j < 4; ++j) {
+                  const float2 o = fadd2(make_float2(v[8 * k + 2 * j], v[8 * k + 2 * j + 1]), make_float2(bf16lo(w4[j]), bf16hi(w4[j])));
+                  v[8 * k + 2 * j] = o.x;
+                  v[8 * k + 2 * j + 1] = o.y;
                 }
+              }
             }
           }
+          // bf16 -> staging (row per thread)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            uint4 o;
+            o.x = pack_bf16x2(v[8 * k + 0], v[8 * k + 1]);
+            o.y = pack_bf16x2(v[8 * k + 2], v[8 * k + 3]);
+            o.z = pack_bf16x2(v[8 * k + 4], v[8 * k + 5]);
+            o.w = pack_bf16x2(v[8 * k + 6], v[8 * k + 7]);
+            *reinterpret_cast<uint4*>(srow + ((static_cast<uint32_t>(k) ^ sw_a) << 4)) = o;
+          }
+          if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
+          __syncwarp();
+          // 4 lanes per row, 8 rows per instruction: 64 contiguous bytes per row
+          bf16* op = reinterpret_cast<bf16*>(sg.out) + (size_t)(c.m0 + q * 32 + brow) * sg.out_ld + sg.out_col + nb + bunit * 8;
+          const size_t out_step = (size_t)8 * sg.out_ld;
+          const int rows_left = p.M - (c.m0 + q * 32 + brow);
+          uint4 f[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t r = k * 8 + brow;     // row within the warp's 32
+            f[k] = *reinterpret_cast<const uint4*>(wstage + r * 64 + ((bunit ^ ((r >> 1) & 3u)) << 4));
+          }
+          if (full_rows) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (k * 8 < rows_left) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
+          }
+          __syncwarp();                          // the staging tile is rewritten by the next chunk
         } else {
-          // unaligned destinations (rare: N or ld not a multiple of 4): scalar path
-#pragma unroll 1
-          for (int k = 0; k < 8; ++k) {
-            const int r = k * 4 + sub;
-            const int mm = c.m0 + q * 32 + r;
-            if (mm >= p.M) continue;
-            const float4 f = *reinterpret_cast<const float4*>(wstage + r * 32 + ((unit ^ (r & 7)) << 2));
-            const float w[4] = {f.x, f.y, f.z, f.w};
-            for (int j = 0; j < 4 && n + j < out_N; ++j) {
-              float x = w[j];
-              if (sg.res) x += __bfloat162float(sg.res[(size_t)mm * sg.res_ld + sg.res_col + n + j]);
-              if (sg.out_fp32)
-                reinterpret_cast<float*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = x;
-              else
-                reinterpret_cast<bf16*>(sg.out)[(size_t)mm * sg.out_ld + sg.out_col + n + j] = __float2bfloat16(x);
+          // row per thread: fp32 outputs, unaligned destinations, the partial chunk of an N tail
+          if (has_res) load_res(ch + 1, rnext);  // keeps the prefetch chain of the vector chunks that may follow
+          if (row_ok) {
+            const size_t o_off = (size_t)m * sg.out_ld + sg.out_col + nb;
+            const int ncol = out_N - nb < 32 ? out_N - nb : 32;
+            if (sg.out_fp32 && ncol == 32 && !has_res && ((sg.out_ld | sg.out_col) & 3) == 0) {
+              float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + o_off);
+#pragma unroll
+              for (int u = 0; u < 8; ++u) o4[u] = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (j < ncol) {
+                  float x = v[j];
+                  if (has_res) x += __bfloat162float(res_row[nb + j]);
+                  if (sg.out_fp32) reinterpret_cast<float*>(sg.out)[o_off + j] = x;
+                  else reinterpret_cast<bf16*>(sg.out)[o_off + j] = __float2bfloat16(x);
+                }
+              }
             }
           }
+          if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
         }
-        __syncwarp();
       }
       __syncwarp();
     }
