@@ -13,7 +13,7 @@ from typing import Dict, Optional
 import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtopo_b200.so")
+LIB_PATH = os.environ.get("TOPO_LIB") or os.path.join(HERE, "libtopo_b200.so")   # TOPO_LIB: another build of the same library (A/B runs)
 
 ACT_NONE, ACT_SILU, ACT_GEGLU, ACT_GELU, ACT_RELU = 0, 1, 2, 3, 4
 

@@ -95,6 +95,15 @@ struct GemmSmem {
   static_assert((W_BYTES % 1024) == 0 || RESID == 0, "resident / W-only stages must keep the 1 KB swizzle alignment");
 };
 
+template <bool B>
+struct BoolC {
+  static constexpr bool value = B;
+};
+template <int I>
+struct IntC {
+  static constexpr int value = I;
+};
+
 struct TileCoord {
   int seg, n0, m0, cw0, ch0, cb0;
 };
@@ -532,11 +541,15 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
 
       // ---- the warp owns rows [q*32, +32) of the tile and every NH-th 32-column output chunk (c32 = hsel, hsel + NH, ...:
       //      a narrow N-tail tile still spreads over the warps).  Per chunk, ROW PER THREAD: TMEM -> registers -> bias /
-      //      per-sample bias / activation / alpha -> + residual (the thread's own 64 bytes of its row, fetched one chunk
-      //      ahead) -> bf16 -> a 2 KB per-warp staging tile (16-byte units XOR-swizzled with (row >> 1) & 3, conflict
+      //      per-sample bias / activation / alpha -> + residual -> bf16 -> a 2 KB per-warp staging tile (16-byte units XOR-swizzled with (row >> 1) & 3, conflict
       //      free both ways); then 4 lanes per row, 8 rows per instruction: 16-byte loads from the staging tile, 16-byte
       //      global stores (64 contiguous bytes per row).  fp32 outputs (rare: eps, VAE image, the ResBlock embedding
       //      table) and chunks that are not 16-byte aligned or not fully inside N go out row per thread.
+      //      The residual comes in the OTHER way round: 4 lanes per row fetch 64 contiguous bytes of 8 rows per instruction
+      //      (one chunk ahead, the first chunk before the accumulator is complete), park them in the staging tile, and every
+      //      thread picks up its own row from there (row-per-thread global loads touched 32 lines per instruction and cost
+      //      the K = 320 projections 15 %).  The tile body is instantiated twice (with / without residual) so that kernels
+      //      without one carry neither the prefetch registers nor the extra shared-memory round trip.
       constexpr int NH = EPI_WARPS / 4;
       const int m = c.m0 + row;
       const bool row_ok = m < p.M;
@@ -563,131 +576,140 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
       uint8_t* srow = wstage + lane * 64;
       const int brow = lane >> 2;                // phase B: row within an 8-row group
       const uint32_t bunit = lane & 3;           // phase B: 16-byte unit (8 columns) within the chunk
-      const bf16* res_row = (has_res && row_ok) ? sg.res + (size_t)m * sg.res_ld + sg.res_col : nullptr;
-      // residual of the thread's row: chunk ch + 1 is fetched while chunk ch is processed (the first one before the
-      // accumulator is even complete)
-      auto load_res = [&](int chn, uint4 (&dst)[4]) {
-        const int nn = out_n0 + (hsel + NH * chn) * 32;
-        if (vec8 && res_row != nullptr && chn < n_my && nn + 32 <= out_N) {
-          const uint4* src = reinterpret_cast<const uint4*>(res_row + nn);
+      const int rows_left = p.M - (c.m0 + q * 32 + brow);
+      const uint32_t sw_b0 = (static_cast<uint32_t>(brow) >> 1) & 3u;   // phase B rows are brow + 8k: (row >> 1) & 3 = sw_b0 ^ 0 (8k keeps bits 1-2)
+      // MODE: 0 = bias + alpha only, 1 = GEGLU, 2 = per-sample bias and / or SiLU, GELU, ReLU.  One instantiation per (RES, MODE):
+      // the loop a launch actually runs is a few KB of contiguous code instead of being spread over a 60 KB body.
+      auto tile_body = [&](auto RESC, auto MODEC) {
+        constexpr bool RES = decltype(RESC)::value;
+        constexpr int MODE = decltype(MODEC)::value;
+        // residual chunk chn in the 4-lanes-per-row layout (rows brow + 8k of the warp's 32, 16-byte unit bunit)
+        auto load_res = [&](int chn, uint4 (&dst)[4]) {
+          const int nn = out_n0 + (hsel + NH * chn) * 32;
+          if (vec8 && chn < n_my && nn + 32 <= out_N) {
+            const bf16* rp = sg.res + (size_t)(c.m0 + q * 32 + brow) * sg.res_ld + sg.res_col + nn + bunit * 8;
+            const size_t rstep = (size_t)8 * sg.res_ld;
 #pragma unroll
-          for (int k = 0; k < 4; ++k) dst[k] = __ldg(src + k);
-        }
-      };
-      uint4 rnext[4];
-      if (has_res) load_res(0, rnext);
-      // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
-      // column group write identical values to identical addresses; a slot of parity `buf` is rewritten only after
-      // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
-      constexpr int MAXJ = (BN / 32 + NH - 1) / NH;
-      float bpre[MAXJ], gpre[MAXJ];
-#pragma unroll
-      for (int j = 0; j < MAXJ; ++j) {
-        const int col = (hsel + NH * j) * 32 + lane;
-        const int nb = c.n0 + col, ng = c.n0 + BN / 2 + col;
-        bpre[j] = (sg.bias && j < n_my && nb < sg.N) ? __ldg(sg.bias + nb) : 0.f;
-        gpre[j] = (geglu && sg.bias && j < n_my && ng < sg.N) ? __ldg(sg.bias + ng) : 0.f;
-      }
-
-      mbar_wait(&tfull[buf], acc_phase);
-      tc_fence_after();
-      if (n_my == 0) {                           // nothing to store from this warp (N tail): release the accumulator
-        tc_fence_before();
-        tempty_arrive(buf);
-        continue;
-      }
-#pragma unroll
-      for (int j = 0; j < MAXJ; ++j) {
-        if (j < n_my) {
-          sbias[(hsel + NH * j) * 32 + lane] = bpre[j];
-          if (geglu) sbias[BN / 2 + (hsel + NH * j) * 32 + lane] = gpre[j];
-        }
-      }
-      __syncwarp();
-      float v[32];
-      tmem_ld32(tmem_acc + lane_addr + hsel * 32, v);   // chunk ch+1 is fetched under the stores of chunk ch
-#pragma unroll 1
-      for (int ch = 0; ch < n_my; ++ch) {
-        const int c32 = hsel + NH * ch;          // 32-column chunk index among the tile's OUTPUT columns
-        const int nb = out_n0 + c32 * 32;        // first output column of the chunk
-        if (geglu) {
-          // gates in two 16-column halves (register budget: 18 warps leave 112 registers per thread)
-          const float2 al2 = make_float2(alpha, alpha);
-          tmem_ld_wait32(v);
-#pragma unroll
-          for (int hf = 0; hf < 2; ++hf) {
-            float g[16];
-            tmem_ld16(tmem_acc + lane_addr + BN / 2 + c32 * 32 + hf * 16, g);
-            tmem_ld_wait();
-            const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32 + hf * 16);
-            const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32 + hf * 16);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {   // packed FP32x2 throughout: the GEGLU epilogue is issue bound (profiles/r01e_geglu.md)
-              const float4 a4 = ba[u], g4 = bg[u];
-              float* vv = v + hf * 16 + 4 * u;
-              const float2 ge0 = gelu_erf2(fadd2(make_float2(g[4 * u + 0], g[4 * u + 1]), make_float2(g4.x, g4.y)));
-              const float2 ge1 = gelu_erf2(fadd2(make_float2(g[4 * u + 2], g[4 * u + 3]), make_float2(g4.z, g4.w)));
-              const float2 o0 = fmul2(fmul2(fadd2(make_float2(vv[0], vv[1]), make_float2(a4.x, a4.y)), ge0), al2);
-              const float2 o1 = fmul2(fmul2(fadd2(make_float2(vv[2], vv[3]), make_float2(a4.z, a4.w)), ge1), al2);
-              vv[0] = o0.x; vv[1] = o0.y; vv[2] = o1.x; vv[3] = o1.y;
-            }
+            for (int k = 0; k < 4; ++k)
+              dst[k] = (full_rows || k * 8 < rows_left) ? __ldg(reinterpret_cast<const uint4*>(rp + k * rstep)) : make_uint4(0u, 0u, 0u, 0u);
           }
-        } else {
-          tmem_ld_wait32(v);
-          const float4* b4 = reinterpret_cast<const float4*>(sbias + c32 * 32);
-          if (plain) {
+        };
+        uint4 rnext[RES ? 4 : 1];
+        if constexpr (RES) load_res(0, rnext);
+        // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
+        // column group write identical values to identical addresses; a slot of parity `buf` is rewritten only after
+        // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
+        constexpr int MAXJ = (BN / 32 + NH - 1) / NH;
+        float bpre[MAXJ], gpre[MAXJ];
+  #pragma unroll
+        for (int j = 0; j < MAXJ; ++j) {
+          const int col = (hsel + NH * j) * 32 + lane;
+          const int nb = c.n0 + col, ng = c.n0 + BN / 2 + col;
+          bpre[j] = (sg.bias && j < n_my && nb < sg.N) ? __ldg(sg.bias + nb) : 0.f;
+          gpre[j] = (geglu && sg.bias && j < n_my && ng < sg.N) ? __ldg(sg.bias + ng) : 0.f;
+        }
+
+        mbar_wait(&tfull[buf], acc_phase);
+        tc_fence_after();
+        if (n_my == 0) {                           // nothing to store from this warp (N tail): release the accumulator
+          tc_fence_before();
+          tempty_arrive(buf);
+          return;
+        }
+  #pragma unroll
+        for (int j = 0; j < MAXJ; ++j) {
+          if (j < n_my) {
+            sbias[(hsel + NH * j) * 32 + lane] = bpre[j];
+            if (geglu) sbias[BN / 2 + (hsel + NH * j) * 32 + lane] = gpre[j];
+          }
+        }
+        __syncwarp();
+        float v[32];
+        tmem_ld32(tmem_acc + lane_addr + hsel * 32, v);   // chunk ch+1 is fetched under the stores of chunk ch
+  #pragma unroll 1
+        for (int ch = 0; ch < n_my; ++ch) {
+          const int c32 = hsel + NH * ch;          // 32-column chunk index among the tile's OUTPUT columns
+          const int nb = out_n0 + c32 * 32;        // first output column of the chunk
+          if constexpr (MODE == 1) {
+            // gates in two 16-column halves (register budget: 18 warps leave 112 registers per thread)
             const float2 al2 = make_float2(alpha, alpha);
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const float4 bb = b4[u];
-              const float2 o0 = fmul2(fadd2(make_float2(v[4 * u], v[4 * u + 1]), make_float2(bb.x, bb.y)), al2);
-              const float2 o1 = fmul2(fadd2(make_float2(v[4 * u + 2], v[4 * u + 3]), make_float2(bb.z, bb.w)), al2);
-              v[4 * u] = o0.x; v[4 * u + 1] = o0.y; v[4 * u + 2] = o1.x; v[4 * u + 3] = o1.y;
+            tmem_ld_wait32(v);
+  #pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              float g[16];
+              tmem_ld16(tmem_acc + lane_addr + BN / 2 + c32 * 32 + hf * 16, g);
+              tmem_ld_wait();
+              const float4* ba = reinterpret_cast<const float4*>(sbias + c32 * 32 + hf * 16);
+              const float4* bg = reinterpret_cast<const float4*>(sbias + BN / 2 + c32 * 32 + hf * 16);
+  #pragma unroll
+              for (int u = 0; u < 4; ++u) {   // packed FP32x2 throughout: the GEGLU epilogue is issue bound (profiles/r01e_geglu.md)
+                const float4 a4 = ba[u], g4 = bg[u];
+                float* vv = v + hf * 16 + 4 * u;
+                const float2 ge0 = gelu_erf2(fadd2(make_float2(g[4 * u + 0], g[4 * u + 1]), make_float2(g4.x, g4.y)));
+                const float2 ge1 = gelu_erf2(fadd2(make_float2(g[4 * u + 2], g[4 * u + 3]), make_float2(g4.z, g4.w)));
+                const float2 o0 = fmul2(fmul2(fadd2(make_float2(vv[0], vv[1]), make_float2(a4.x, a4.y)), ge0), al2);
+                const float2 o1 = fmul2(fmul2(fadd2(make_float2(vv[2], vv[3]), make_float2(a4.z, a4.w)), ge1), al2);
+                vv[0] = o0.x; vv[1] = o0.y; vv[2] = o1.x; vv[3] = o1.y;
+              }
             }
           } else {
-            const bool rb_vec = rb && ((reinterpret_cast<uintptr_t>(rb + nb) & 15) == 0) && nb + 32 <= out_N;
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-              const float4 bb = b4[u];
-              float x[4] = {v[4 * u] + bb.x, v[4 * u + 1] + bb.y, v[4 * u + 2] + bb.z, v[4 * u + 3] + bb.w};
-              if (rb_vec) {
-                const float4 r4 = __ldg(reinterpret_cast<const float4*>(rb + nb) + u);
-                x[0] += r4.x; x[1] += r4.y; x[2] += r4.z; x[3] += r4.w;
-              } else if (rb) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                  if (nb + 4 * u + j < out_N) x[j] += __ldg(rb + nb + 4 * u + j);
+            tmem_ld_wait32(v);
+            const float4* b4 = reinterpret_cast<const float4*>(sbias + c32 * 32);
+            if constexpr (MODE == 0) {
+              const float2 al2 = make_float2(alpha, alpha);
+  #pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const float4 bb = b4[u];
+                const float2 o0 = fmul2(fadd2(make_float2(v[4 * u], v[4 * u + 1]), make_float2(bb.x, bb.y)), al2);
+                const float2 o1 = fmul2(fadd2(make_float2(v[4 * u + 2], v[4 * u + 3]), make_float2(bb.z, bb.w)), al2);
+                v[4 * u] = o0.x; v[4 * u + 1] = o0.y; v[4 * u + 2] = o1.x; v[4 * u + 3] = o1.y;
               }
-              if (silu) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) x[j] = silu_f(x[j]);
-              } else if (gelu) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) x[j] = gelu_erf_f(x[j]);
-              } else if (relu) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) x[j] = fmaxf(x[j], 0.f);
+            } else {
+              const bool rb_vec = rb && ((reinterpret_cast<uintptr_t>(rb + nb) & 15) == 0) && nb + 32 <= out_N;
+  #pragma unroll
+              for (int u = 0; u < 8; ++u) {
+                const float4 bb = b4[u];
+                float x[4] = {v[4 * u] + bb.x, v[4 * u + 1] + bb.y, v[4 * u + 2] + bb.z, v[4 * u + 3] + bb.w};
+                if (rb_vec) {
+                  const float4 r4 = __ldg(reinterpret_cast<const float4*>(rb + nb) + u);
+                  x[0] += r4.x; x[1] += r4.y; x[2] += r4.z; x[3] += r4.w;
+                } else if (rb) {
+  #pragma unroll
+                  for (int j = 0; j < 4; ++j)
+                    if (nb + 4 * u + j < out_N) x[j] += __ldg(rb + nb + 4 * u + j);
+                }
+                if (silu) {
+  #pragma unroll
+                  for (int j = 0; j < 4; ++j) x[j] = silu_f(x[j]);
+                } else if (gelu) {
+  #pragma unroll
+                  for (int j = 0; j < 4; ++j) x[j] = gelu_erf_f(x[j]);
+                } else if (relu) {
+  #pragma unroll
+                  for (int j = 0; j < 4; ++j) x[j] = fmaxf(x[j], 0.f);
+                }
+  #pragma unroll
+                for (int j = 0; j < 4; ++j) v[4 * u + j] = x[j] * alpha;
               }
-#pragma unroll
-              for (int j = 0; j < 4; ++j) v[4 * u + j] = x[j] * alpha;
             }
           }
-        }
-        if (ch == n_my - 1) {
-          tc_fence_before();
-          tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+NBUF into it
-        }
-        const bool chunk_vec = vec8 && nb + 32 <= out_N;
-        if (chunk_vec) {
-          if (has_res) {
-            uint4 rr[4];
+          if (ch == n_my - 1) {
+            tc_fence_before();
+            tempty_arrive(buf);                    // accumulator drained: the MMA warp may start tile it+NBUF into it
+          }
+          const bool chunk_vec = vec8 && nb + 32 <= out_N;
+          if (chunk_vec) {
+            if constexpr (RES) {
+              // residual rows: registers (4 lanes per row) -> staging tile -> own row
 #pragma unroll
-            for (int k = 0; k < 4; ++k) rr[k] = rnext[k];
-            load_res(ch + 1, rnext);
-            if (row_ok) {
+              for (int k = 0; k < 4; ++k)
+                *reinterpret_cast<uint4*>(wstage + (k * 8 + brow) * 64 + ((bunit ^ sw_b0) << 4)) = rnext[k];
+              __syncwarp();
+              load_res(ch + 1, rnext);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint32_t w4[4] = {rr[k].x, rr[k].y, rr[k].z, rr[k].w};
+                const uint4 w = *reinterpret_cast<const uint4*>(srow + ((static_cast<uint32_t>(k) ^ sw_a) << 4));
+                const uint32_t w4[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                   const float2 o = fadd2(make_float2(v[8 * k + 2 * j], v[8 * k + 2 * j + 1]), make_float2(bf16lo(w4[j]), bf16hi(w4[j])));
@@ -695,65 +717,73 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
                   v[8 * k + 2 * j + 1] = o.y;
                 }
               }
+              // (no barrier: a thread overwrites only the row it has just read)
             }
-          }
-          // bf16 -> staging (row per thread)
+            // bf16 -> staging (row per thread)
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            uint4 o;
-            o.x = pack_bf16x2(v[8 * k + 0], v[8 * k + 1]);
-            o.y = pack_bf16x2(v[8 * k + 2], v[8 * k + 3]);
-            o.z = pack_bf16x2(v[8 * k + 4], v[8 * k + 5]);
-            o.w = pack_bf16x2(v[8 * k + 6], v[8 * k + 7]);
-            *reinterpret_cast<uint4*>(srow + ((static_cast<uint32_t>(k) ^ sw_a) << 4)) = o;
-          }
-          if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
-          __syncwarp();
-          // 4 lanes per row, 8 rows per instruction: 64 contiguous bytes per row
-          bf16* op = reinterpret_cast<bf16*>(sg.out) + (size_t)(c.m0 + q * 32 + brow) * sg.out_ld + sg.out_col + nb + bunit * 8;
-          const size_t out_step = (size_t)8 * sg.out_ld;
-          const int rows_left = p.M - (c.m0 + q * 32 + brow);
-          uint4 f[4];
+            for (int k = 0; k < 4; ++k) {
+              uint4 o;
+              o.x = pack_bf16x2(v[8 * k + 0], v[8 * k + 1]);
+              o.y = pack_bf16x2(v[8 * k + 2], v[8 * k + 3]);
+              o.z = pack_bf16x2(v[8 * k + 4], v[8 * k + 5]);
+              o.w = pack_bf16x2(v[8 * k + 6], v[8 * k + 7]);
+              *reinterpret_cast<uint4*>(srow + ((static_cast<uint32_t>(k) ^ sw_a) << 4)) = o;
+            }
+            if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
+            __syncwarp();
+            // 4 lanes per row, 8 rows per instruction: 64 contiguous bytes per row
+            bf16* op = reinterpret_cast<bf16*>(sg.out) + (size_t)(c.m0 + q * 32 + brow) * sg.out_ld + sg.out_col + nb + bunit * 8;
+            const size_t out_step = (size_t)8 * sg.out_ld;
+            uint4 f[4];
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint32_t r = k * 8 + brow;     // row within the warp's 32
-            f[k] = *reinterpret_cast<const uint4*>(wstage + r * 64 + ((bunit ^ ((r >> 1) & 3u)) << 4));
-          }
-          if (full_rows) {
+            for (int k = 0; k < 4; ++k) f[k] = *reinterpret_cast<const uint4*>(wstage + (k * 8 + brow) * 64 + ((bunit ^ sw_b0) << 4));
+            if (full_rows) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
-          } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              if (k * 8 < rows_left) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
-          }
-          __syncwarp();                          // the staging tile is rewritten by the next chunk
-        } else {
-          // row per thread: fp32 outputs, unaligned destinations, the partial chunk of an N tail
-          if (has_res) load_res(ch + 1, rnext);  // keeps the prefetch chain of the vector chunks that may follow
-          if (row_ok) {
-            const size_t o_off = (size_t)m * sg.out_ld + sg.out_col + nb;
-            const int ncol = out_N - nb < 32 ? out_N - nb : 32;
-            if (sg.out_fp32 && ncol == 32 && !has_res && ((sg.out_ld | sg.out_col) & 3) == 0) {
-              float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(sg.out) + o_off);
-#pragma unroll
-              for (int u = 0; u < 8; ++u) o4[u] = make_float4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+              for (int k = 0; k < 4; ++k) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                if (j < ncol) {
-                  float x = v[j];
-                  if (has_res) x += __bfloat162float(res_row[nb + j]);
-                  if (sg.out_fp32) reinterpret_cast<float*>(sg.out)[o_off + j] = x;
-                  else reinterpret_cast<bf16*>(sg.out)[o_off + j] = __float2bfloat16(x);
-                }
+              for (int k = 0; k < 4; ++k)
+                if (k * 8 < rows_left) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
+            }
+            __syncwarp();                          // the staging tile is rewritten by the next chunk
+          } else {
+            // row per thread, compact (rare: fp32 outputs, unaligned destinations, the partial chunk of an N tail): the
+            // thread parks 16 columns at a time in its own staging row and walks them in a rolled loop
+            if constexpr (RES) load_res(ch + 1, rnext);  // keeps the prefetch chain of the vector chunks that may follow
+            const size_t o_off = (size_t)m * sg.out_ld + sg.out_col + nb;
+            const bf16* res_row = RES ? sg.res + (size_t)m * sg.res_ld + sg.res_col + nb : nullptr;
+            float4* sr4 = reinterpret_cast<float4*>(srow);
+            const float* sr = reinterpret_cast<const float*>(srow);
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) sr4[u] = make_float4(v[16 * hf + 4 * u], v[16 * hf + 4 * u + 1], v[16 * hf + 4 * u + 2], v[16 * hf + 4 * u + 3]);
+              int ncol = out_N - nb - 16 * hf;
+              ncol = row_ok ? (ncol > 16 ? 16 : ncol) : 0;
+#pragma unroll 1
+              for (int j = 0; j < ncol; ++j) {
+                float x = sr[j];
+                if constexpr (RES) x += __bfloat162float(res_row[16 * hf + j]);
+                if (sg.out_fp32) reinterpret_cast<float*>(sg.out)[o_off + 16 * hf + j] = x;
+                else reinterpret_cast<bf16*>(sg.out)[o_off + 16 * hf + j] = __float2bfloat16(x);
               }
             }
+            if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
+            __syncwarp();
           }
-          if (ch + 1 < n_my) tmem_ld32(tmem_acc + lane_addr + (c32 + NH) * 32, v);
         }
+        __syncwarp();
+      };
+      const int mode = geglu ? 1 : (plain ? 0 : 2);
+      if (has_res) {
+        if (mode == 0) tile_body(BoolC<true>{}, IntC<0>{});
+        else if (mode == 1) tile_body(BoolC<true>{}, IntC<1>{});
+        else tile_body(BoolC<true>{}, IntC<2>{});
+      } else {
+        if (mode == 0) tile_body(BoolC<false>{}, IntC<0>{});
+        else if (mode == 1) tile_body(BoolC<false>{}, IntC<1>{});
+        else tile_body(BoolC<false>{}, IntC<2>{});
       }
-      __syncwarp();
     }
   }
 
