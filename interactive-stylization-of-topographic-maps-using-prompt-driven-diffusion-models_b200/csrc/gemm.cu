@@ -1047,6 +1047,22 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
     for (int i = 0; i < n_seg; ++i) all192 = all192 && segs[i].N % 192 == 0 && segs[i].act == TOPO_ACT_NONE;
     if (all192) BN = 192;
   }
+  // fused q/k/v of the 32x32 (3 x 640) and 16x16 (3 x 1280) levels: 160- / 256-wide tiles instead of 128-wide ones
+  // (TOPO_MULTI_WIDE=0 disables, A/B runs)
+  static const bool multi_wide = [] { const char* e = getenv("TOPO_MULTI_WIDE"); return !(e && e[0] == '0'); }();
+  if (multi_wide && n_seg > 1 && segs[0].r_pad == 0 && BN == 128) {
+    bool all256 = true, all160 = true;
+    int nt256 = 0, nt160 = 0;
+    for (int i = 0; i < n_seg; ++i) {
+      all256 = all256 && segs[i].N % 256 == 0 && segs[i].act == TOPO_ACT_NONE;
+      all160 = all160 && segs[i].N % 160 == 0 && segs[i].act == TOPO_ACT_NONE;
+      nt256 += segs[i].N / 256;
+      nt160 += segs[i].N / 160;
+    }
+    const int mt = (M + BM - 1) / BM;
+    if (all256 && mt * nt256 >= 2 * sm_count()) BN = 256;
+    else if (all160 && mt * nt160 >= 2 * sm_count()) BN = 160;
+  }
   // N = 384 (padded-head q projection of the 64x64 level), K <= 320: two 192-wide tiles with W resident
   if ((resident_mask() & 1) && n_seg == 1 && segs[0].r_pad == 0 && segs[0].act != TOPO_ACT_GEGLU && segs[0].N == 384 && K <= 320 &&
       (M + BM - 1) / BM >= sm_count())
@@ -1136,6 +1152,15 @@ int conv3x3_dispatch(const void* x, int B, int H, int W, int C, int x_ld, const 
     bn192 = (e && e[0] == '1') ? 1 : 0;
   }
   if (pair && bn192 && seg->N == 320) BN = 192;   // n tiles 192 + 128 instead of 256 + 64 (measured: no gain)
+  // 8x8 level (19 row tiles): 10 x 5 = 50 pair tiles of 256 columns leave a third of the 74 clusters idle for the whole
+  // kernel; 10 x 7 = 70 tiles of 192 columns run in the same single wave with 3/4 of the work per cluster.
+  // TOPO_CONV_WAVE192=0 disables (A/B runs)
+  static const bool wave192 = [] { const char* e = getenv("TOPO_CONV_WAVE192"); return !(e && e[0] == '0'); }();
+  if (pair && wave192 && BN == 256 && seg->N > 256) {
+    const int clusters = sm_count() / 2, pm = (B * H * W + 2 * BM - 1) / (2 * BM);
+    const int t256 = pm * ((seg->N + 255) / 256), t192 = pm * ((seg->N + 191) / 192);
+    if (t256 < clusters && t192 <= clusters) BN = 192;
+  }
   if (pair && !bn192 && seg->N == 320 && bn320_enabled()) BN = 320;
   GemmParams p;
   memset(&p, 0, sizeof(p));

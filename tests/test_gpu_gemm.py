@@ -208,3 +208,33 @@ def test_resident_x_fused_qkv_with_bias_and_ragged_tail():
     ops.lora_linear_raw(x, M, K, K, segs)
     assert capi.last_kernel() == "gemm_resident_kernel<192, 4, -5>", capi.last_kernel()
     assert_close(out, torch.cat([x.float() @ W.float().t() + b for W, b in zip(Ws, bs)], 1), TOL, "resident-x fused qkv")
+
+
+@pytest.mark.parametrize("M,K,N,kernel", [
+    (9728, 1280, 1280, "gemm_kernel<256, 0, 4, 0, 0>"),      # 16x16 level: 256-wide tiles over three segments
+    (38912, 640, 640, "gemm_kernel<160, 0, 5, 0, 0>"),       # 32x32 level: four 160-wide tiles per segment
+])
+def test_fused_qkv_wide_tiles(M, K, N, kernel):
+    from topo_b200 import capi
+    ops = _ops()
+    x = rnd(M, K, seed=1).to(BF16)
+    out = torch.zeros(M, 3 * N, dtype=BF16, device="cuda")
+    Ws = [rnd(N, K, seed=10 + i, scale=K ** -0.5).to(BF16) for i in range(3)]
+    segs = [capi.make_linear(W, out, N, out_ld=3 * N, out_col=i * N) for i, W in enumerate(Ws)]
+    ops.lora_linear_raw(x, M, K, K, segs)
+    assert capi.last_kernel() == kernel, capi.last_kernel()
+    assert_close(out, torch.cat([x.float() @ W.float().t() for W in Ws], 1), TOL, f"fused qkv {M}x{K}x3x{N}")
+
+
+def test_conv3x3_single_wave_192_wide_pair_tiles():
+    """8x8 level at the bench batch (38 x 64 = 19 row tiles): 70 pair tiles of 192 columns instead of 50 of 256."""
+    from topo_b200 import capi
+    ops = _ops()
+    B, H, W, Cin, Cout = 38, 8, 8, 1280, 1280
+    x = rnd(B, H, W, Cin, seed=1).to(BF16)
+    w = rnd(Cout, Cin, 3, 3, seed=2, scale=(9 * Cin) ** -0.5).to(BF16)
+    b = rnd(Cout, seed=3)
+    y = ops.conv3x3(x, w, b)
+    assert capi.last_kernel() == "gemm_kernel<192, 0, 6, 1, 1>", capi.last_kernel()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), b, padding=1).permute(0, 2, 3, 1)
+    assert_close(y, ref, TOL, "conv3x3 8x8 192-wide pair tiles")

@@ -23,7 +23,9 @@ for k,v in rows.items():
     a=min(v.get("A",[0])); b=min(v.get("B",[0]))
     print(f"{k:52s} A {a:8.1f}  B {b:8.1f}  {100*(b/a-1) if a else 0:+6.1f}%")
 PY
-for v in A B; do
+for r in 1 2; do for v in A B; do
   if [ $v = A ]; then export TOPO_LIB=$PWD/$PK/ab/libtopo_A.so; else unset TOPO_LIB; fi
-  timeout 300 python tools/shape_breakdown.py > gpurun_out/${tag}_shape_breakdown_$v.txt 2>&1; echo "$v $(head -1 gpurun_out/${tag}_shape_breakdown_$v.txt)"
-done
+  timeout 300 python tools/shape_breakdown.py > gpurun_out/${tag}_shape_breakdown_$v$r.txt 2>&1; echo "$v$r $(head -1 gpurun_out/${tag}_shape_breakdown_$v$r.txt)"
+done; done
+unset TOPO_LIB
+python tools/ab_breakdown.py gpurun_out/${tag}_shape_breakdown_A1.txt gpurun_out/${tag}_shape_breakdown_B1.txt gpurun_out/${tag}_shape_breakdown_A2.txt gpurun_out/${tag}_shape_breakdown_B2.txt | tee gpurun_out/${tag}_ab_breakdown.txt

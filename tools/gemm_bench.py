@@ -75,6 +75,8 @@ def qkv_case(M, N, K):
 Be = 38
 gemm_case(Be * 4096, 384, 320)
 qkv_case(Be * 4096, 384, 320)
+qkv_case(Be * 1024, 640, 640)
+qkv_case(Be * 256, 1280, 1280)
 gemm_case(Be * 4096, 320, 320, res=True)
 gemm_case(Be * 4096, 320, 320)
 gemm_case(Be * 4096, 320, 384, res=True)
