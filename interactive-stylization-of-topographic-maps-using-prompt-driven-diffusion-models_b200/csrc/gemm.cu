@@ -583,19 +583,24 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
       auto tile_body = [&](auto RESC, auto MODEC) {
         constexpr bool RES = decltype(RESC)::value;
         constexpr int MODE = decltype(MODEC)::value;
-        // residual chunk chn in the 4-lanes-per-row layout (rows brow + 8k of the warp's 32, 16-byte unit bunit)
-        auto load_res = [&](int chn, uint4 (&dst)[4]) {
+        // residual chunk chn: cp.async straight into the staging tile in the 4-lanes-per-row layout (rows brow + 8k of the
+        // warp's 32, 16-byte unit bunit).  No registers are held across the accumulator wait / the previous chunk (a
+        // register prefetch was spilled to local memory at 96 registers per thread, which put the load latency AND a
+        // local-memory round trip on the critical path: profiles/r02s).  The staging tile must be free: issued at the top of
+        // the tile and after the store phase of the previous chunk.  Rows past M keep stale data (never stored).
+        auto issue_res = [&](int chn) {
           const int nn = out_n0 + (hsel + NH * chn) * 32;
           if (vec8 && chn < n_my && nn + 32 <= out_N) {
             const bf16* rp = sg.res + (size_t)(c.m0 + q * 32 + brow) * sg.res_ld + sg.res_col + nn + bunit * 8;
             const size_t rstep = (size_t)8 * sg.res_ld;
+            uint8_t* dst = wstage + brow * 64 + ((bunit ^ sw_b0) << 4);
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              dst[k] = (full_rows || k * 8 < rows_left) ? __ldg(reinterpret_cast<const uint4*>(rp + k * rstep)) : make_uint4(0u, 0u, 0u, 0u);
+              if (full_rows || k * 8 < rows_left) cp_async16(dst + k * 8 * 64, rp + k * rstep);
           }
+          cp_async_commit();
         };
-        uint4 rnext[RES ? 4 : 1];
-        if constexpr (RES) load_res(0, rnext);
+        if constexpr (RES) issue_res(0);
         // bias of this warp's chunks: global -> registers before the wait, -> smem after it.  The four warps of one
         // column group write identical values to identical addresses; a slot of parity `buf` is rewritten only after
         // tfull of tile it (which needs every warp's tempty arrival for tile it-2, i.e. its last read of that slot).
@@ -700,12 +705,9 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           const bool chunk_vec = vec8 && nb + 32 <= out_N;
           if (chunk_vec) {
             if constexpr (RES) {
-              // residual rows: registers (4 lanes per row) -> staging tile -> own row
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
-                *reinterpret_cast<uint4*>(wstage + (k * 8 + brow) * 64 + ((bunit ^ sw_b0) << 4)) = rnext[k];
+              // residual rows: landed in the staging tile (4 lanes per row) -> own row
+              cp_async_wait_all();
               __syncwarp();
-              load_res(ch + 1, rnext);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint4 w = *reinterpret_cast<const uint4*>(srow + ((static_cast<uint32_t>(k) ^ sw_a) << 4));
@@ -746,10 +748,11 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
                 if (k * 8 < rows_left) *reinterpret_cast<uint4*>(op + k * out_step) = f[k];
             }
             __syncwarp();                          // the staging tile is rewritten by the next chunk
+            if constexpr (RES) issue_res(ch + 1);
           } else {
             // row per thread, compact (rare: fp32 outputs, unaligned destinations, the partial chunk of an N tail): the
             // thread parks 16 columns at a time in its own staging row and walks them in a rolled loop
-            if constexpr (RES) load_res(ch + 1, rnext);  // keeps the prefetch chain of the vector chunks that may follow
+            if constexpr (RES) cp_async_wait_all();      // (a vector chunk never follows a row-per-thread one: nothing new to fetch)
             const size_t o_off = (size_t)m * sg.out_ld + sg.out_col + nb;
             const bf16* res_row = RES ? sg.res + (size_t)m * sg.res_ld + sg.res_col + nb : nullptr;
             float4* sr4 = reinterpret_cast<float4*>(srow);
