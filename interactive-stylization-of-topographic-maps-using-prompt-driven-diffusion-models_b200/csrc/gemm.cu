@@ -108,6 +108,37 @@ struct TileCoord {
   int seg, n0, m0, cw0, ch0, cb0;
 };
 
+// (row tile, n tile counted over all segments) -> coordinates
+template <int BN, bool CONV>
+__device__ __forceinline__ TileCoord tile_coord_mn(const GemmParams& p, int mt, int nt) {
+  TileCoord c;
+  int sgi = 0;
+#pragma unroll
+  for (int i = 0; i < MAX_SEG - 1; ++i) {
+    if (sgi == i && i + 1 < p.n_seg && nt >= p.seg[i].n_tiles) {
+      nt -= p.seg[i].n_tiles;
+      sgi = i + 1;
+    }
+  }
+  c.seg = sgi;
+  c.n0 = nt * BN;
+  c.cw0 = c.ch0 = c.cb0 = 0;
+  if (CONV) {
+    int t = mt;
+    const int tw = t % p.tiles_w;
+    t /= p.tiles_w;
+    const int th = t % p.tiles_h;
+    const int tb = t / p.tiles_h;
+    c.cw0 = tw * p.bw;
+    c.ch0 = th * p.bh;
+    c.cb0 = tb * p.bb;
+    c.m0 = (c.cb0 * p.H + c.ch0) * p.W + c.cw0;
+  } else {
+    c.m0 = mt * BM;
+  }
+  return c;
+}
+
 // tile id -> (segment, n tile, m tile); m fastest so concurrently running CTAs share one W tile and stream x.
 template <int BN, bool CONV>
 __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
@@ -117,14 +148,7 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmParams& p, int tile) {
     // n fastest: the tiles that share an x (A) tile are consecutive, every CTA walks a contiguous chunk of the list,
     // so x is streamed from HBM exactly once (the W tiles are small and stay in L2)
     mt = tile / p.nt_total;
-    nt = tile - mt * p.nt_total;
-#pragma unroll
-    for (int i = 0; i < MAX_SEG - 1; ++i) {
-      if (sgi == i && i + 1 < p.n_seg && nt >= p.seg[i].n_tiles) {
-        nt -= p.seg[i].n_tiles;
-        sgi = i + 1;
-      }
-    }
+    return tile_coord_mn<BN, CONV>(p, mt, tile - mt * p.nt_total);
   } else {
 #pragma unroll
     for (int i = 0; i < MAX_SEG - 1; ++i) {
@@ -493,10 +517,28 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
     };
     const int row = q * 32 + lane;
     const uint32_t lane_addr = static_cast<uint32_t>(q * 32) << 16;
-    int it = 0;
     int g_epi = 0;   // LoRA: index of the latest T this warp has converted
-    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
-      const TileCoord c = tile_coord<BN, CONV>(p, tile_id(tile));
+    // n-fastest order: the (row tile, n tile) pair is advanced incrementally (sixteen warps each paid an integer division
+    // per tile: profiles/r02s)
+    const bool inc = p.nt_total > 0;
+    int w_mt = 0, w_nt = 0, s_mt = 0, s_nt = 0;
+    if (inc) {
+      w_mt = tile_begin / p.nt_total;
+      w_nt = tile_begin - w_mt * p.nt_total;
+      s_mt = tile_step / p.nt_total;
+      s_nt = tile_step - s_mt * p.nt_total;
+    }
+    const int n_it = tile_begin < tile_end ? (tile_end - tile_begin + tile_step - 1) / tile_step : 0;
+    for (int it = 0; it < n_it; ++it) {
+      const TileCoord c = inc ? tile_coord_mn<BN, CONV>(p, PAIR ? 2 * w_mt + rank : w_mt, w_nt)
+                              : tile_coord<BN, CONV>(p, tile_id(tile_begin + it * tile_step));
+      int x_mt = w_mt + s_mt, x_nt = w_nt + s_nt;   // the next tile of this CTA
+      if (inc && x_nt >= p.nt_total) {
+        x_nt -= p.nt_total;
+        ++x_mt;
+      }
+      w_mt = x_mt;
+      w_nt = x_nt;
       const GemmSegDev& sg = p.seg[c.seg];
       const int buf = NBUF == 2 ? (it & 1) : 0;
       const uint32_t acc_phase = NBUF == 2 ? ((it >> 1) & 1) : (it & 1);
@@ -533,8 +575,9 @@ __device__ __forceinline__ void gemm_body(const GemmParams& p) {
           mbar_arrive(t_ready);
         };
         if (it == 0) convert_t(0, sg.s);
-        if (tile + tile_step < tile_end) {
-          const TileCoord cn = tile_coord<BN, CONV>(p, tile_id(tile + tile_step));
+        if (it + 1 < n_it) {
+          const TileCoord cn = inc ? tile_coord_mn<BN, CONV>(p, PAIR ? 2 * x_mt + rank : x_mt, x_nt)
+                                   : tile_coord<BN, CONV>(p, tile_id(tile_begin + (it + 1) * tile_step));
           if (cn.m0 != c.m0 || cn.seg != c.seg) convert_t(++g_epi, p.seg[cn.seg].s);
         }
       }
