@@ -750,7 +750,8 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
 
   if (warp == 0) {
     // ===================== TMA producer: K/V per segment (double buffered), the query tiles through a ring ==========
-    if (lane == 0) {
+    {   // whole warp, warp-uniform control flow: operands stay in uniform registers; one elected lane issues
+      const bool lead = elect_one();
       int seg_loaded = -1;
       for (int i = 0; i < n; ++i) {
         const long long g = g0 + i;
@@ -760,26 +761,27 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
         if (seg != seg_loaded) {
           const int u = seg & 1;
           mbar_wait(&kv_empty[u], ((seg >> 1) & 1) ^ 1);
-          mbar_expect_tx(&kv_full[u], 2 * L::KV_BYTES);
+          if (lead) mbar_expect_tx(&kv_full[u], 2 * L::KV_BYTES);
           uint8_t* kd = kv_buf + u * 2 * L::KV_BYTES;
 #pragma unroll
           for (int a = 0; a < ATOMS; ++a) {
-            tma_load_3d(kd + a * L::KV_ATOM, &p.tm_k, &kv_full[u], col0 + a * 64, 0, b);
-            tma_load_3d(kd + L::KV_BYTES + a * L::KV_ATOM, &p.tm_v, &kv_full[u], col0 + a * 64, 0, b);
+            if (lead) tma_load_3d(kd + a * L::KV_ATOM, &p.tm_k, &kv_full[u], col0 + a * 64, 0, b);
+            if (lead) tma_load_3d(kd + L::KV_BYTES + a * L::KV_ATOM, &p.tm_v, &kv_full[u], col0 + a * 64, 0, b);
           }
           seg_loaded = seg;
         }
         const int qs = i % QS;
         mbar_wait(&q_empty[qs], ((i / QS) & 1) ^ 1);
-        mbar_expect_tx(&q_full[qs], L::Q_BYTES);
+        if (lead) mbar_expect_tx(&q_full[qs], L::Q_BYTES);
 #pragma unroll
         for (int a = 0; a < ATOMS; ++a)
-          tma_load_3d(q_ring + qs * L::Q_BYTES + a * L::Q_ATOM, &p.tm_q, &q_full[qs], col0 + a * 64, tile * ATT_BM, b);
+          if (lead) tma_load_3d(q_ring + qs * L::Q_BYTES + a * L::Q_ATOM, &p.tm_q, &q_full[qs], col0 + a * 64, tile * ATT_BM, b);
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {   // whole warp, warp-uniform control flow: operands stay in uniform registers; one elected lane issues
+      const bool lead = elect_one();
       constexpr uint32_t idesc_s = make_idesc_bf16(128, XA_NKP, 0, 0);
       constexpr uint32_t idesc_pv = make_idesc_bf16(128, DP, 0, 1);  // B (= V) is MN-major
       int seg_ready = -1;   // highest segment whose K/V this thread has already waited for
@@ -799,10 +801,10 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
         for (int k = 0; k < DP / 16; ++k) {
           const uint64_t qd = kmajor_desc(q_s + (k >> 2) * L::Q_ATOM + (k & 3) * 32, 128);
           const uint64_t kd = kmajor_desc(k_s + (k >> 2) * L::KV_ATOM + (k & 3) * 32, 128);
-          umma_bf16(tmem_s, qd, kd, idesc_s, k != 0);
+          if (lead) umma_bf16(tmem_s, qd, kd, idesc_s, k != 0);
         }
-        umma_commit(&s_full[i % NWG]);
-        umma_commit(&q_empty[qs]);
+        if (lead) umma_commit(&s_full[i % NWG]);
+        if (lead) umma_commit(&q_empty[qs]);
       };
       for (int i = 0; i < NWG && i < n; ++i) issue_s(i);
       for (int i = 0; i < n; ++i) {
@@ -815,11 +817,11 @@ cross_attention_kernel(const __grid_constant__ AttnParams p, int tiles_per_group
         const uint32_t tmem_o = tmem_p + L::O_COL;
 #pragma unroll
         for (int k = 0; k < XA_NKP / 16; ++k)   // A = P straight from TMEM: 16 keys = 8 packed columns per step
-          umma_bf16_ts(tmem_o, tmem_p + k * 8, mnmajor_sw128_desc(v_s + k * 2048, L::KV_ATOM), idesc_pv, k != 0);
-        umma_commit(&o_full[slot]);
+          if (lead) umma_bf16_ts(tmem_o, tmem_p + k * 8, mnmajor_sw128_desc(v_s + k * 2048, L::KV_ATOM), idesc_pv, k != 0);
+        if (lead) umma_commit(&o_full[slot]);
         // last tile of its K/V segment: the buffer is free once everything issued so far has finished (the S of later
         // segments issued ahead read the OTHER buffer)
-        if (i + 1 == n || seg_of(i + 1) != seg) umma_commit(&kv_empty[u]);
+        if (i + 1 == n || seg_of(i + 1) != seg) if (lead) umma_commit(&kv_empty[u]);
         // S of this slot's NEXT tile goes in right behind P V (the tensor pipe executes in issue order, so it overwrites P
         // only after P V has consumed it); the warpgroup is still storing O(i) when it completes
         if (i + NWG < n) issue_s(i + NWG);
