@@ -21,5 +21,5 @@ run attn    'attention_split_kernel|attention_kernel<\(int\)(80|160), \(int\)2' 
 run xattn   'cross_attention_kernel' 0 6
 run gn      'gn_(stats|apply|small)_kernel' 0 8
 run ln      'layernorm' 0 4
-run conv    'gemm_kernel<\(int\)(256|320), \(int\)0, \(int\)[0-9], \(bool\)1, \(bool\)1>' 2 4
-run proj    'gemm_kernel<\(int\)(128|160|192|256), \(int\)0, \(int\)[0-9], \(bool\)0, \(bool\)[01]>' 8 10
+run conv    'gemm_kernel<\(int\)(192|256|320), \(int\)0, \(int\)[0-9], \(bool\)1, \(bool\)1>' 2 6
+run proj    'gemm_resident_kernel|gemm_kernel<\(int\)(128|160|192|256), \(int\)0, \(int\)[0-9], \(bool\)0, \(bool\)[01]>' 8 16
