@@ -57,9 +57,9 @@ def peaks():
 
 
 def ncu_table():
-    """profiles/r02_ncu.json (tools/ncu_named.sh + tools/ncu_summary.py json): per kernel template instance, the mean
+    """profiles/r03_ncu.json (tools/ncu_named.sh + tools/ncu_summary.py json): per kernel template instance, the mean
     of `ncu --set full` metrics over the captured launches of the FINAL build.  None when the file is absent."""
-    p = os.path.join(ROOT, "profiles", "r02_ncu.json")
+    p = os.path.join(ROOT, "profiles", "r03_ncu.json")
     return json.load(open(p)) if os.path.exists(p) else None
 
 
@@ -205,9 +205,9 @@ def roofline_leg(E, eng, model, pk, ctx_d, hints_d, xT_d):
     roof = {"bound": r["bound"], "kernel": top, "achieved": r["achieved"], "peak": pk["tf_sust"] if r["bound"] == "tensor" else pk["hbm"],
             "unit": r["unit"], "frac": r["frac"],
             "traffic": nk["dram_bytes_per_launch"] if nk else None,
-            "traffic_source": (f"profiles/r02_ncu.json ({ncu.get('source', 'ncu --set full')}): mean dram__bytes_read.sum + "
+            "traffic_source": (f"profiles/r03_ncu.json ({ncu.get('source', 'ncu --set full')}): mean dram__bytes_read.sum + "
                                f"dram__bytes_write.sum over {nk['launches']} captured launches of this kernel") if nk else
-                              "no ncu capture of this kernel in profiles/r02_ncu.json",
+                              "no ncu capture of this kernel in profiles/r03_ncu.json",
             "peak_source": pk["src"] + (" (sustained bf16)" if r["bound"] == "tensor" else " (copy)"),
             "launches": d["launches"], "avg_launch_us": 1e3 * d["ms"] / d["launches"],
             "algorithmic_per_launch": (d["flops"] if r["bound"] == "tensor" else d["bytes"]) / d["launches"],

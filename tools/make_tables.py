@@ -26,15 +26,18 @@ if d:
     if d.get("cpu_baseline"):
         print(f"CPU arm (oracle port, {d['cpu_baseline']['cores']} host threads): {d['cpu_baseline']['value']:.4f} tiles/s.")
     print()
+    mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    ncu_all = json.load(open(os.path.join(P, "r03_ncu.json")))["kernels"]
     print("Per kernel template instance, one instrumented eager `apply_model` (Be = 38), CUDA events per launch; `frac` = achieved ÷ measured peak "
-          "(sustained bf16 1403 TFLOP/s or copy 6538 GB/s); ncu columns from `profiles/r02_ncu.json` (same build):\n")
+          f"(sustained bf16 {mp['bf16_tflops_sustained']:.0f} TFLOP/s or copy {mp['hbm_gbs']:.0f} GB/s, MEASURED_PEAKS.json); ncu columns from "
+          "`profiles/r03_ncu.json` (`ncu --set full` of the same build):\n")
     print("| kernel | ops | launches | ms | share | achieved | frac | ncu tensor-pipe % | ncu DRAM % | ncu DRAM MB/launch |")
     print("|---|---|---:|---:|---:|---:|---:|---:|---:|---:|")
     tot = sum(v["ms"] for v in r["by_kernel"].values())
     for k, v in r["by_kernel"].items():
         if v["ms"] < 0.12:
             continue
-        n = v.get("ncu", {})
+        n = ncu_all.get(k, {})
         print(f"| `{k}` | {', '.join(v['ops'])} | {v['launches']} | {v['ms']:.2f} | {100 * v['ms'] / tot:.1f} % | {v['achieved']:.0f} {v['unit']} | {v['frac']:.2f} | "
               f"{n.get('tensor_pipe_pct', '—')} | {n.get('dram_pct', '—')} | {('%.0f' % (n['dram_bytes_per_launch'] / 1e6)) if n else '—'} |")
     print(f"\nBy op class: " + "; ".join(f"{k} {v['ms']:.2f} ms ({v['achieved']:.0f} {v['unit']}, {v['frac']:.2f})" for k, v in r["by_op"].items() if v["ms"] > 0.3) + ".")

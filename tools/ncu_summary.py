@@ -21,6 +21,7 @@ def rows_of(path):
 
 
 def short(name):
+    name = re.sub(r"\((int|bool|unsigned int)\)", "", name)   # negative template arguments keep their cast: "(int)-5"
     name = re.sub(r"\(.*", "", name)
     return name.replace("void ", "").strip()
 
