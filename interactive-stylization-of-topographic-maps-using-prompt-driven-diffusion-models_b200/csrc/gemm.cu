@@ -1125,8 +1125,25 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   // tile per cluster; short-K projections are epilogue bound and lose from coupling two epilogues to one issuer
   // (measured: K = 1280 / 2560 -> +5 / +9 %, K = 320 GEGLU -> -16 %)
   static const int pair_min_k = [] { const char* e = getenv("TOPO_PAIR_MINK"); return e ? atoi(e) : 1024; }();   // A/B runs
-  const bool pair = BN == 256 && r_pad == 0 && K >= pair_min_k && pair_enabled() &&
-                    ((M + 2 * BM - 1) / (2 * BM)) >= sm_count() / 2;
+  bool pair = BN == 256 && r_pad == 0 && K >= pair_min_k && pair_enabled() &&
+              ((M + 2 * BM - 1) / (2 * BM)) >= sm_count() / 2;
+  // 192-wide pair tiles (TOPO_PAIR192=0 disables, A/B runs):
+  //  * N = 320 at K >= 1024 (feed-forward output of the 64x64 level): 192 + 128 columns instead of 256 + a 64-wide tail whose
+  //    UMMA runs at the A-fetch rate and reloads all of x for a fifth of the columns;
+  //  * the long-K projections of the 8x8 level (19 row tiles x 1280 columns): 10 x 7 = 70 pair tiles fill the 74 clusters
+  //    in ONE wave, against two waves of 190 single-CTA 128-wide tiles.
+  static const bool pair192 = [] { const char* e = getenv("TOPO_PAIR192"); return !(e && e[0] == '0'); }();
+  if (pair192 && pair_enabled() && r_pad == 0 && n_seg == 1 && segs[0].act != TOPO_ACT_GEGLU && K >= pair_min_k) {
+    const int pm = (M + 2 * BM - 1) / (2 * BM), clusters = sm_count() / 2;
+    if (pair && segs[0].N == 320) BN = 192;
+    else if (!pair && segs[0].N > 256) {
+      const int t192 = pm * ((segs[0].N + 191) / 192);
+      if (t192 <= clusters && 2 * t192 > clusters) {   // a single wave that fills more than half of the clusters
+        BN = 192;
+        pair = true;
+      }
+    }
+  }
   // the 320-wide single-accumulator tile pays on the 45+-block K loops of the convs (273 -> 247 us) but not here: with
   // K = 1280 the un-overlapped epilogue costs more than the second A load (152 -> 160 us); TOPO_BN320=2 forces it
   const bool wide320 = pair && n_seg == 1 && segs[0].N == 320 && segs[0].act != TOPO_ACT_GEGLU && bn320_force_gemm();
@@ -1146,6 +1163,7 @@ int gemm_dispatch(const void* x, int M, int K, int x_ld, const topo_linear_t* se
   for (int i = 0; i < n_seg; ++i) p.total_tiles += p.seg[i].n_tiles * p.m_tiles;
   dim3 grid(p.total_tiles);
   if (wide320) return launch_gemm_pair<320, 5, false>(p, st);
+  if (pair && BN == 192) return launch_gemm_pair<192, 6, false>(p, st);
   if (pair) return launch_gemm_pair<256, 6, false>(p, st);
   // short-K projections of the 64x64 level: one operand resident in shared memory (see GemmSmem)
   if (r_pad == 0 && K <= 384 && p.total_tiles >= 2 * sm_count()) {

@@ -238,3 +238,19 @@ def test_conv3x3_single_wave_192_wide_pair_tiles():
     assert capi.last_kernel() == "gemm_kernel<192, 0, 6, 1, 1>", capi.last_kernel()
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float(), b, padding=1).permute(0, 2, 3, 1)
     assert_close(y, ref, TOL, "conv3x3 8x8 192-wide pair tiles")
+
+
+@pytest.mark.parametrize("M,K,N,res", [
+    (2432, 1280, 1280, True),        # 8x8 level: 10 x 7 pair tiles in one wave (tail n tile 128 wide)
+    (2432 - 70, 5120, 1280, False),  # ragged M, long K
+    (148 * 128 + 33, 1280, 320, True),   # feed-forward output of the 64x64 level: 192 + 128 columns
+])
+def test_pair_tiles_192_wide_projection(M, K, N, res):
+    from topo_b200 import capi
+    ops = _ops()
+    x, W = rnd(M, K, seed=1).to(BF16), rnd(N, K, seed=2, scale=K ** -0.5).to(BF16)
+    b = rnd(N, seed=3)
+    rs = rnd(M, N, seed=4).to(BF16) if res else None
+    y = ops.linear(x, W, b, res=rs)
+    assert capi.last_kernel() == "gemm_kernel<192, 0, 6, 0, 1>", capi.last_kernel()
+    assert_close(y, x.float() @ W.float().t() + b + (rs.float() if res else 0), TOL, f"192-wide pair tiles M{M} K{K} N{N}")

@@ -82,6 +82,8 @@ gemm_case(Be * 4096, 320, 320)
 gemm_case(Be * 4096, 320, 384, res=True)
 gemm_case(Be * 4096, 2560, 320, act=2)
 gemm_case(Be * 4096, 320, 1280, res=True)
+gemm_case(Be * 64, 1280, 1280, res=True)
+gemm_case(Be * 64, 1280, 5120, res=True)
 gemm_case(Be * 1024, 5120, 640, act=2)
 gemm_case(Be * 1024, 640, 640, res=True)
 gemm_case(Be * 1024, 640, 2560, res=True)
