@@ -2,17 +2,22 @@
 //
 //   out = alpha * ( x W^T  +  s (x A^T) B^T  + bias + rowbias ) + res          (optionally SiLU / GEGLU)
 //
-//  * one CTA per SM walks a static tile list (tile = blockIdx.x + i * gridDim.x); three pipelines run concurrently:
-//      warp 0      TMA producer   : x / W / LoRA-A tiles -> 4-stage smem ring (SWIZZLE_128B, K-major); x is a 2-D row
-//                                   tile or a 4-D NHWC box shifted per filter tap (implicit-GEMM 3x3 conv; TMA
-//                                   out-of-bounds zero fill is the conv padding).  Runs ahead across tile boundaries.
+//  * one CTA per SM walks a static tile list; three pipelines run concurrently (18 warps):
+//      warp 0      TMA producer   : x / W / LoRA-A tiles -> smem ring (SWIZZLE_128B, K-major); x is a 2-D row tile or a 4-D
+//                                   NHWC box shifted per filter tap (implicit-GEMM 3x3 conv; TMA out-of-bounds zero fill is
+//                                   the conv padding).  Runs ahead across tile boundaries.
 //      warp 1      MMA issuer     : UMMA M=128, N=BN, K=16 into one of TWO fp32 accumulators in TMEM, so the epilogue
-//                                   of tile i overlaps the main loop of tile i+1
-//      warps 2..9  epilogue       : TMEM -> registers (tcgen05.ld 32x32b; two warps per TMEM lane quadrant, each half of
-//                                   the columns), bias / per-sample bias / activation, fp32 staging tile in smem
-//                                   (XOR-swizzled 16-byte units), then row-contiguous residual loads + stores to an
-//                                   arbitrary (ld, column offset) destination: q/k/v, concat buffers and the ControlNet
-//                                   zero-conv residual are written in place.
+//                                   of tile i overlaps the main loop of tile i+1.
+//                                   Both warps walk their loops WHOLE-WARP (warp-uniform control flow keeps descriptors,
+//                                   coordinates and barrier addresses in uniform registers) and one elected lane issues.
+//      warps 2..17 epilogue       : four warps per TMEM lane quadrant, each every fourth 32-column chunk.  Row per thread:
+//                                   TMEM -> registers (tcgen05.ld 32x32b), bias / per-sample bias / activation, + residual
+//                                   (rows brought into the warp's 2 KB staging tile by cp.async), -> bf16 -> staging tile
+//                                   (XOR-swizzled 16-byte units) -> 16-byte coalesced stores to an arbitrary (ld, column
+//                                   offset) destination: q/k/v, concat buffers and the ControlNet zero-conv residual are
+//                                   written in place.  The tile body is instantiated per (residual, mode) so that the loop
+//                                   a launch runs is a few KB of straight code.
+//  * gemm_resident_kernel: short-K projections with one operand resident in shared memory (see GemmSmem).
 //  * LoRA: T = x A^T (N = r_pad) of a (row tile, segment) group goes into a third TMEM region in a short PRE-PASS over K
 //    (x tile + LoRA-A tile through the same ring, the LoRA-A tile in the W slot) that the issuer runs ONE TILE AHEAD of the
 //    group's first tile; the epilogue warps move s*T (bf16) TMEM->smem while that earlier tile's main loop is still
